@@ -1,0 +1,188 @@
+/*
+ * mpenv.h -- C ABI of libmpenv_b200.so: the B200-native replacement for the
+ * per-step simulation path of MadronaMPEnv's Manager (reference src/mgr.hpp).
+ *
+ * Each entry point names the reference interface it replaces.  Plain pointers
+ * and sizes only; no C++ or torch types cross this boundary.  One handle = one
+ * GPU = one CUDA stream; calls on a handle are not re-entrant (the reference
+ * Manager is single-threaded per instance, mgr.hpp:31-161).  Multi-GPU = one
+ * handle per device, each created with its own world_id_offset.
+ *
+ * All functions return MPENV_OK (0) or a negative error code; the message is
+ * available from mpenv_last_error().  (The reference FATALs / aborts on these
+ * conditions, mgr.cpp:204-206, 1855.)
+ */
+#ifndef MPENV_H
+#define MPENV_H
+
+#include <stdint.h>
+#include "mpenv_state.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MPENV_OK 0
+#define MPENV_ERR_INVALID (-1)   /* bad argument / unsupported configuration */
+#define MPENV_ERR_IO (-2)        /* asset file missing or corrupt */
+#define MPENV_ERR_CUDA (-3)      /* CUDA runtime error (no device, OOM, launch failure) */
+
+/* Task (reference src/types.hpp:45-51); only MPENV_TASK_ZONE is implemented. */
+#define MPENV_TASK_EXPLORE 0
+#define MPENV_TASK_TDM 1
+#define MPENV_TASK_ZONE 2
+#define MPENV_TASK_TURRET 3
+#define MPENV_TASK_ZONE_CAPTURE_DEFEND 4
+
+/* SimFlags (reference src/sim_flags.hpp:7-21). */
+#define MPENV_FLAG_DEFAULT 0u
+#define MPENV_FLAG_SPAWN_IN_MIDDLE (1u << 0)
+#define MPENV_FLAG_RANDOMIZE_HP_MAGAZINE (1u << 1)
+#define MPENV_FLAG_NAVMESH_SPAWN (1u << 2)
+#define MPENV_FLAG_NO_RESPAWN (1u << 3)
+#define MPENV_FLAG_STAGGER_STARTS (1u << 4)
+#define MPENV_FLAG_ENABLE_CURRICULUM (1u << 5)
+#define MPENV_FLAG_HARDCODED_SPAWNS (1u << 6)
+#define MPENV_FLAG_RANDOM_FLIP_TEAMS (1u << 7)
+#define MPENV_FLAG_STATIC_FLIP_TEAMS (1u << 8)
+#define MPENV_FLAG_FULL_TEAM_POLICY (1u << 9)
+#define MPENV_FLAG_SIM_EVAL_MODE (1u << 10)
+#define MPENV_FLAG_SUBZONES (1u << 11)
+
+/* Replaces Manager::Config (mgr.hpp:33-52) + MapConfig (mgr.hpp:15-23). */
+typedef struct mpenv_config {
+    int32_t gpu_id;              /* Config::gpuID */
+    uint32_t num_worlds;         /* Config::numWorlds (worlds on THIS device) */
+    uint32_t rand_seed;          /* Config::randSeed */
+    int32_t auto_reset;          /* Config::autoReset */
+    uint32_t sim_flags;          /* Config::simFlags */
+    uint32_t task_type;          /* Config::taskType; must be MPENV_TASK_ZONE */
+    uint32_t team_size;          /* Config::teamSize; must be 6 */
+    uint32_t num_pbt_policies;   /* Config::numPBTPolicies (carried, unused by the step) */
+    uint32_t policy_history_size;/* Config::policyHistorySize (carried, unused) */
+    const char *scene_dir;       /* directory holding collisions/spawns/zones.bin
+                                    (bindings.cpp:58-76 derives the four file names from it) */
+    uint32_t world_id_offset;    /* global id of local world 0: the episode RNG key is
+                                    split_i(initKey, episode, GLOBAL world id) (sim.cpp:743-746),
+                                    so shards of one big batch reproduce it world for world */
+    uint32_t enable_full_team;   /* also fill the FullTeam* tensors every step (sim.cpp:3054-3301) */
+} mpenv_config;
+
+typedef struct mpenv_handle mpenv_handle;
+
+/* Tensor export ids = reference ExportID (src/sim.hpp:15-66). */
+enum mpenv_export_id {
+    MPENV_EXPORT_RESET = 0, MPENV_EXPORT_WORLD_CURRICULUM, MPENV_EXPORT_EXPLORE_ACTION,
+    MPENV_EXPORT_PVP_DISCRETE_ACTION, MPENV_EXPORT_PVP_AIM_ACTION,
+    MPENV_EXPORT_PVP_DISCRETE_AIM_ACTION, MPENV_EXPORT_REWARD, MPENV_EXPORT_DONE,
+    MPENV_EXPORT_MATCH_RESULT, MPENV_EXPORT_AGENT_POLICY, MPENV_EXPORT_SELF_OBSERVATION,
+    MPENV_EXPORT_TEAMMATE_OBSERVATIONS, MPENV_EXPORT_OPPONENT_OBSERVATIONS,
+    MPENV_EXPORT_OPPONENT_LAST_KNOWN_OBSERVATIONS, MPENV_EXPORT_SELF_POSITION_OBSERVATION,
+    MPENV_EXPORT_TEAMMATE_POSITION_OBSERVATIONS, MPENV_EXPORT_OPPONENT_POSITION_OBSERVATIONS,
+    MPENV_EXPORT_OPPONENT_LAST_KNOWN_POSITION_OBSERVATIONS, MPENV_EXPORT_OPPONENT_MASKS,
+    MPENV_EXPORT_FWD_LIDAR, MPENV_EXPORT_REAR_LIDAR, MPENV_EXPORT_AGENT_MAP,
+    MPENV_EXPORT_UNMASKED_AGENT_MAP, MPENV_EXPORT_HP, MPENV_EXPORT_ALIVE, MPENV_EXPORT_MAGAZINE,
+    MPENV_EXPORT_FULL_TEAM_ACTIONS, MPENV_EXPORT_FULL_TEAM_GLOBAL, MPENV_EXPORT_FULL_TEAM_PLAYERS,
+    MPENV_EXPORT_FULL_TEAM_ENEMIES, MPENV_EXPORT_FULL_TEAM_LAST_KNOWN_ENEMIES,
+    MPENV_EXPORT_FULL_TEAM_FWD_LIDAR, MPENV_EXPORT_FULL_TEAM_REAR_LIDAR,
+    MPENV_EXPORT_FULL_TEAM_REWARD, MPENV_EXPORT_FULL_TEAM_DONE,
+    MPENV_EXPORT_FULL_TEAM_POLICY_ASSIGNMENTS, MPENV_EXPORT_EVENT_LOG,
+    MPENV_EXPORT_PACKED_STEP_SNAPSHOT, MPENV_EXPORT_FILTERS_STATE_OBSERVATION,
+    MPENV_EXPORT_REWARD_HYPER_PARAMS, MPENV_NUM_EXPORTS,
+    MPENV_EXPORT_SIM_CONTROL = 1000  /* Manager::simControlTensor (mgr.cpp:287-293) */
+};
+
+#define MPENV_DTYPE_I32 0
+#define MPENV_DTYPE_F32 1
+
+/* Replaces madrona::py::Tensor(ptr, dtype, dims, gpuID) (mgr.cpp:295-301):
+ * a raw DEVICE pointer owned by the handle, stable for its lifetime, row-major,
+ * leading dimension world-major then agent. */
+typedef struct mpenv_tensor_desc {
+    void *dev_ptr;
+    int32_t dtype;
+    int32_t ndim;
+    int64_t dims[4];
+    int32_t gpu_id;
+} mpenv_tensor_desc;
+
+/* Manager::Manager(cfg) (mgr.cpp:1914-1919 -> Impl::init mgr.cpp:1213): loads the
+ * map, builds the BVH, allocates device state and constructs every world
+ * (Sim::Sim, sim.cpp:5850).  Fails with MPENV_ERR_CUDA when no CUDA device is
+ * usable -- there is no CPU execution path. */
+int mpenv_create(const mpenv_config *cfg, mpenv_handle **out);
+/* Manager::~Manager */
+void mpenv_destroy(mpenv_handle *h);
+/* Manager::init (mgr.cpp:1923-1946): force a reset of every world, run the Init
+ * graph (reset + observations), return when results are visible. */
+int mpenv_init(mpenv_handle *h);
+/* Manager::step (mgr.cpp:1948-1951): one simulation step, synchronous. */
+int mpenv_step(mpenv_handle *h);
+/* Stream-ordered variants, no host synchronisation: the kernel sequence of
+ * gpuStreamInit / gpuStreamStep (mgr.cpp:507-645) without the buffer copies.
+ * `cuda_stream` is a cudaStream_t. */
+int mpenv_init_async(mpenv_handle *h, void *cuda_stream);
+int mpenv_step_async(mpenv_handle *h, void *cuda_stream);
+/* Manager::gpuStreamInit / gpuStreamStep (mgr.cpp:507-645): copy the
+ * train-interface inputs from `buffers` into the sim tensors, run, copy the
+ * outputs back, all on `cuda_stream`.  Buffer order = mpenv_train_interface(). */
+int mpenv_stream_init(mpenv_handle *h, void *cuda_stream, void **buffers);
+int mpenv_stream_step(mpenv_handle *h, void *cuda_stream, void **buffers);
+/* Waits for the handle's own stream. */
+int mpenv_sync(mpenv_handle *h);
+/* Manager::*Tensor() exporters (mgr.cpp:1965-2381). */
+int mpenv_tensor(mpenv_handle *h, uint32_t export_id, mpenv_tensor_desc *out);
+
+/* Manager::trainInterface (mgr.cpp:2383-2431): the named input / output tensors
+ * in the order the stream entry points expect their buffers. */
+typedef struct mpenv_named_tensor {
+    const char *name;
+    uint32_t export_id;
+    int32_t is_input;
+} mpenv_named_tensor;
+int mpenv_train_interface(mpenv_handle *h, const mpenv_named_tensor **out, uint32_t *count);
+
+/* Manager::triggerReset / setPvPAction / setHP / setUniformAgentPolicy
+ * (mgr.cpp:2484-2658): small host->device writes used by drivers and tests. */
+int mpenv_trigger_reset(mpenv_handle *h, int32_t world_idx);
+int mpenv_set_pvp_action(mpenv_handle *h, int32_t world_idx, int32_t agent_idx,
+                         const int32_t discrete[4], const float aim[2], const int32_t discrete_aim[2]);
+int mpenv_set_hp(mpenv_handle *h, int32_t world_idx, int32_t agent_idx, int32_t hp);
+int mpenv_set_uniform_agent_policy(mpenv_handle *h, int32_t policy_idx);
+
+/* Per-device reduction of episode statistics for the multi-GPU allreduce
+ * (new).  Writes MPENV_NUM_STATS int64 values to a device buffer
+ * owned by the handle and returns its pointer; stream-ordered. */
+#define MPENV_NUM_STATS 16
+int mpenv_episode_stats_async(mpenv_handle *h, void *cuda_stream, int64_t **dev_out);
+
+/* Test / debug surface: full per-world state (see mpenv_state.h). */
+int mpenv_get_world_state(mpenv_handle *h, uint32_t world_idx, mpenv_world_state *out);
+/* Number of kernel launches issued by one step / one init (for bench accounting). */
+int mpenv_launches_per_step(mpenv_handle *h, uint32_t *step_launches, uint32_t *init_launches);
+
+const char *mpenv_last_error(mpenv_handle *h);   /* h may be NULL: last create() error */
+
+/* ---- map section: host-side asset loading (Impl::init's loadMapData /
+ * loadMapSpawnData / loadMapZones, mgr.cpp:1228-1236, 1360) ---------------- */
+typedef struct mpenv_map mpenv_map;
+typedef struct mpenv_map_info_t {
+    uint32_t num_nodes, num_tris, num_leaves;
+    float root_aabb[6];
+    float world_bounds[6];
+    uint32_t num_a_spawns, num_b_spawns, num_respawns, num_zones;
+} mpenv_map_info_t;
+int mpenv_map_load(const char *scene_dir, mpenv_map **out);
+void mpenv_map_free(mpenv_map *m);
+int mpenv_map_info(const mpenv_map *m, mpenv_map_info_t *info);
+/* num_nodes x 64-byte nodes in the reference MeshBVH::Node layout (mesh_bvh.hpp:61-86) */
+const void *mpenv_map_nodes(const mpenv_map *m);
+/* (num_tris + 1) x 3 x 3 floats: de-indexed triangle positions in leaf order */
+const float *mpenv_map_verts(const mpenv_map *m);
+const char *mpenv_map_last_error(void);
+
+#ifdef __cplusplus
+}
+#endif
+
+#endif

@@ -1,0 +1,497 @@
+"""ctypes plumbing shared by the tests, __graft_entry__.smoke() and bench.py's
+CPU-baseline leg: the oracle (reference sim code under oracle/shim), the
+hostsim harness (device stage functions compiled for the host, tests only) and
+the product library (libmpenv_b200.so, CUDA only).
+
+Nothing here is imported by the product package.
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+SCENE = os.path.join(ROOT, "data", "simple_map")
+ORACLE_DIR = os.path.join(ROOT, "oracle")
+REF_SO = os.path.join(ORACLE_DIR, "_ref", "libmpenv_ref.so")
+REF_DET_SO = os.path.join(ORACLE_DIR, "_ref", "libmpenv_ref_det.so")
+DET_MATH_SO = os.path.join(ORACLE_DIR, "_ref", "libdet_math.so")
+HOSTSIM_SO = os.path.join(ROOT, "tests", "hostsim", "_build", "libhostsim.so")
+PRODUCT_SO = os.path.join(ROOT, "madrona-mp-env_b200", "libmpenv_b200.so")
+CSRC = os.path.join(ROOT, "madrona-mp-env_b200", "csrc")
+
+AGENTS = 12
+
+# reference ExportID (src/sim.hpp:15-66)
+EXPORT_IDS = dict(
+    reset=0, world_curriculum=1, explore_action=2, pvp_discrete_action=3, pvp_aim_action=4,
+    pvp_discrete_aim_action=5, reward=6, done=7, match_result=8, agent_policy=9,
+    self_obs=10, teammate_obs=11, opponent_obs=12, opponent_last_known_obs=13,
+    self_pos=14, teammate_pos=15, opponent_pos=16, opponent_last_known_pos=17,
+    opponent_masks=18, fwd_lidar=19, rear_lidar=20, agent_map=21, unmasked_agent_map=22,
+    hp=23, alive=24, magazine=25, full_team_actions=26, full_team_global=27,
+    full_team_players=28, full_team_enemies=29, full_team_last_known_enemies=30,
+    full_team_fwd_lidar=31, full_team_rear_lidar=32, full_team_reward=33, full_team_done=34,
+    full_team_policy=35, event_log=36, packed_step_snapshot=37, filters_state_obs=38,
+    reward_hyper_params=39,
+)
+# per-row float/int32 counts and dtype; rows: 'agent' (W*12), 'world' (W), 'team' (W*2)
+EXPORT_SHAPES = dict(
+    reset=("world", 1, np.int32), world_curriculum=("world", 1, np.int32),
+    pvp_discrete_action=("agent", 4, np.int32), pvp_aim_action=("agent", 2, np.float32),
+    pvp_discrete_aim_action=("agent", 2, np.int32), reward=("agent", 1, np.float32),
+    done=("agent", 1, np.int32), match_result=("world", 30, np.int32),
+    agent_policy=("agent", 1, np.int32), self_obs=("agent", 43, np.float32),
+    teammate_obs=("agent", 5 * 32, np.float32), opponent_obs=("agent", 6 * 32, np.float32),
+    opponent_last_known_obs=("agent", 6 * 32, np.float32), self_pos=("agent", 3, np.float32),
+    teammate_pos=("agent", 15, np.float32), opponent_pos=("agent", 18, np.float32),
+    opponent_last_known_pos=("agent", 18, np.float32), opponent_masks=("agent", 6, np.float32),
+    fwd_lidar=("agent", 2 * 32 * 4, np.float32), rear_lidar=("agent", 2 * 8 * 4, np.float32),
+    hp=("agent", 1, np.float32), alive=("agent", 1, np.float32), magazine=("agent", 2, np.int32),
+    full_team_global=("team", 16, np.float32), full_team_players=("team", 6 * 28, np.float32),
+    full_team_enemies=("team", 6 * 33, np.float32),
+    full_team_last_known_enemies=("team", 6 * 24, np.float32),
+    full_team_fwd_lidar=("team", 6 * 256, np.float32), full_team_rear_lidar=("team", 6 * 64, np.float32),
+    full_team_reward=("team", 1, np.float32), full_team_done=("team", 1, np.int32),
+    filters_state_obs=("agent", 1, np.float32), reward_hyper_params=("agent", 9, np.float32),
+)
+# the train-interface outputs (mgr.cpp:2398-2431) + exported state
+STEP_OUTPUTS = [
+    "self_obs", "teammate_obs", "opponent_obs", "opponent_last_known_obs", "self_pos",
+    "teammate_pos", "opponent_pos", "opponent_last_known_pos", "opponent_masks", "fwd_lidar",
+    "rear_lidar", "hp", "alive", "magazine", "filters_state_obs", "reward", "done", "match_result",
+    "reward_hyper_params",
+]
+FULL_TEAM_OUTPUTS = [
+    "full_team_global", "full_team_players", "full_team_enemies", "full_team_last_known_enemies",
+    "full_team_fwd_lidar", "full_team_rear_lidar", "full_team_reward", "full_team_done",
+]
+
+
+def rows_of(kind, num_worlds):
+    return {"agent": num_worlds * AGENTS, "world": num_worlds, "team": num_worlds * 2}[kind]
+
+
+# ---------------------------------------------------------------- world state
+class AgentState(C.Structure):
+    _fields_ = [
+        ("pos", C.c_float * 3), ("rot", C.c_float * 4), ("vel", C.c_float * 3),
+        ("move_new_pos", C.c_float * 3), ("move_new_vel", C.c_float * 3), ("move_max_vel", C.c_float),
+        ("aim_yaw", C.c_float), ("aim_pitch", C.c_float), ("aim_rot", C.c_float * 4),
+        ("hp", C.c_float), ("alive", C.c_float), ("mag_bullets", C.c_int32), ("mag_reloading", C.c_int32),
+        ("dmg", C.c_float * 6), ("pose_cur", C.c_int32), ("pose_tgt", C.c_int32),
+        ("pose_transition", C.c_int32), ("rng_key", C.c_uint32 * 2), ("rng_count", C.c_uint32),
+        ("landed_shot_on", C.c_int32), ("remaining_respawn_steps", C.c_int32),
+        ("remaining_autoheal_steps", C.c_int32), ("successful_kill", C.c_int32),
+        ("was_shot_count", C.c_int32), ("was_killed", C.c_int32), ("fired_shot_t", C.c_float),
+        ("in_zone", C.c_int32), ("min_dist_to_zone", C.c_float), ("has_died", C.c_int32),
+        ("reloaded_full_mag", C.c_int32), ("weapon_type", C.c_int32),
+        ("crumb_total_penalty", C.c_float), ("crumb_steps_since_new", C.c_int32),
+        ("crumb_last", C.c_int32), ("start_pos", C.c_float * 3), ("explore_new_cells", C.c_uint32),
+        ("can_see", C.c_int32 * 6), ("team", C.c_int32), ("team_offset", C.c_int32),
+        ("policy", C.c_int32), ("reward_coefs", C.c_float * 9),
+    ]
+
+
+class CrumbState(C.Structure):
+    _fields_ = [("pos", C.c_float * 3), ("penalty", C.c_float), ("team", C.c_int32),
+                ("team_offset", C.c_int32)]
+
+
+class WorldState(C.Structure):
+    _fields_ = [
+        ("team_a", C.c_int32), ("cur_step", C.c_int32), ("is_finished", C.c_int32),
+        ("enable_spawn_curriculum", C.c_int32), ("cur_curriculum_tier", C.c_uint32),
+        ("cur_curriculum_spawn_idx", C.c_uint32),
+        ("zone_cur", C.c_int32), ("zone_controlling_team", C.c_int32), ("zone_contested", C.c_int32),
+        ("zone_captured", C.c_int32), ("zone_earned_point", C.c_int32),
+        ("zone_steps_remaining", C.c_int32), ("zone_steps_until_point", C.c_int32),
+        ("match_result", C.c_int32 * 30), ("zone_stats", C.c_int32 * 25),
+        ("base_rng_key", C.c_uint32 * 2), ("base_rng_count", C.c_uint32),
+        ("cur_episode_idx", C.c_uint32), ("world_episode_counter", C.c_uint32),
+        ("world_curriculum", C.c_int32), ("reset_flag", C.c_int32),
+        ("filters_active", C.c_uint64 * 2), ("filters_last_matches", (C.c_int32 * 3) * 2),
+        ("filters_last_matched_step", C.c_int32 * 2),
+        ("goal_min_dist", C.c_float * 2), ("goal_team_step_rewards", C.c_float * 2),
+        ("team_rewards", C.c_float * 2),
+        ("spawn_a_last_used", C.c_uint32 * 128), ("spawn_b_last_used", C.c_uint32 * 128),
+        ("respawn_last_used", C.c_uint32 * 128),
+        ("num_breadcrumbs", C.c_int32), ("breadcrumbs", CrumbState * 192),
+        ("agents", AgentState * 12),
+    ]
+
+
+def struct_to_dict(s):
+    out = {}
+    for name, _ in s._fields_:
+        v = getattr(s, name)
+        if isinstance(v, C.Structure):
+            out[name] = struct_to_dict(v)
+        elif isinstance(v, C.Array):
+            if issubclass(v._type_, C.Structure):
+                out[name] = [struct_to_dict(x) for x in v]
+            else:
+                out[name] = np.ctypeslib.as_array(v).copy()
+        else:
+            out[name] = v
+    return out
+
+
+# Fields whose float values are compared bit-for-bit by their int32 view.
+def diff_world_state(a, b, path="", float_tol=0.0, skip=()):
+    """Returns a list of 'path: a != b' strings for differing leaves."""
+    diffs = []
+    for k in a:
+        p = f"{path}.{k}" if path else k
+        if any(p.endswith(s) for s in skip):
+            continue
+        va, vb = a[k], b[k]
+        if isinstance(va, dict):
+            diffs += diff_world_state(va, vb, p, float_tol, skip)
+        elif isinstance(va, list):
+            for i, (xa, xb) in enumerate(zip(va, vb)):
+                diffs += diff_world_state(xa, xb, f"{p}[{i}]", float_tol, skip)
+        elif isinstance(va, np.ndarray):
+            if va.dtype.kind == "f":
+                if float_tol == 0.0:
+                    same = np.array_equal(va.view(np.int32), vb.view(np.int32)) or np.array_equal(va, vb)
+                else:
+                    same = np.allclose(va, vb, rtol=float_tol, atol=float_tol)
+            else:
+                same = np.array_equal(va, vb)
+            if not same:
+                diffs.append(f"{p}: {va} != {vb}")
+        elif isinstance(va, float):
+            if float_tol == 0.0:
+                same = (va == vb) or (va != va and vb != vb)
+            else:
+                same = abs(va - vb) <= float_tol * max(1.0, abs(va), abs(vb))
+            if not same:
+                diffs.append(f"{p}: {va!r} != {vb!r}")
+        else:
+            if va != vb:
+                diffs.append(f"{p}: {va} != {vb}")
+    return diffs
+
+
+# --------------------------------------------------------------------- builds
+def _run(cmd, cwd=None):
+    r = subprocess.run(cmd, cwd=cwd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    if r.returncode != 0:
+        raise RuntimeError(f"build failed: {' '.join(cmd)}\n{r.stdout[-4000:]}")
+
+
+def _stale(target, sources):
+    if not os.path.exists(target):
+        return True
+    t = os.path.getmtime(target)
+    return any(os.path.exists(s) and os.path.getmtime(s) > t for s in sources)
+
+
+def _csrc_files():
+    return [os.path.join(CSRC, f) for f in os.listdir(CSRC)] + [
+        os.path.join(ROOT, "include", "mpenv.h"), os.path.join(ROOT, "include", "mpenv_state.h")]
+
+
+def build_hostsim():
+    src = [os.path.join(ROOT, "tests", "hostsim", "hostsim.cpp")] + _csrc_files()
+    if _stale(HOSTSIM_SO, src):
+        os.makedirs(os.path.dirname(HOSTSIM_SO), exist_ok=True)
+        _run(["g++", "-std=c++17", "-O2", "-march=x86-64-v3", "-ffp-contract=off", "-fno-fast-math",
+              "-fPIC", "-shared", "-o", HOSTSIM_SO,
+              os.path.join(ROOT, "tests", "hostsim", "hostsim.cpp"),
+              os.path.join(CSRC, "assets.cpp"), os.path.join(CSRC, "map_capi.cpp")])
+    return HOSTSIM_SO
+
+
+def build_oracle():
+    """Builds oracle/_ref/*.so when /root/reference is present (this container);
+    on the GPU box the prebuilt files travel with the snapshot."""
+    have = all(os.path.exists(p) for p in (REF_SO, REF_DET_SO, DET_MATH_SO))
+    if os.path.isdir("/root/reference/src"):
+        deps = [os.path.join(ORACLE_DIR, f) for f in ("ref_driver.cpp", "det_math_override.h",
+                "det_math_probe.cpp", "shim/shim_core.cpp", "shim/madrona/shim_core.hpp",
+                "shim/madrona/geo.hpp", "Makefile")] + [os.path.join(CSRC, "mp_math.h")]
+        if not have or any(_stale(p, deps) for p in (REF_SO, REF_DET_SO, DET_MATH_SO)):
+            _run(["make", "-j4"], cwd=ORACLE_DIR)
+    elif not have:
+        raise RuntimeError("oracle/_ref is missing and /root/reference is not available to build it")
+    return REF_SO, REF_DET_SO
+
+
+# ---------------------------------------------------------------------- map
+class MapInfo(C.Structure):
+    _fields_ = [("num_nodes", C.c_uint32), ("num_tris", C.c_uint32), ("num_leaves", C.c_uint32),
+                ("root_aabb", C.c_float * 6), ("world_bounds", C.c_float * 6),
+                ("num_a_spawns", C.c_uint32), ("num_b_spawns", C.c_uint32),
+                ("num_respawns", C.c_uint32), ("num_zones", C.c_uint32)]
+
+
+def load_map(lib, scene=SCENE):
+    """Returns (nodes u8[num_nodes,64], verts f32[num_tris*3,3], info) using the
+    mpenv_map_* C ABI of `lib` (hostsim or the product library)."""
+    lib.mpenv_map_load.argtypes = [C.c_char_p, C.POINTER(C.c_void_p)]
+    lib.mpenv_map_info.argtypes = [C.c_void_p, C.POINTER(MapInfo)]
+    lib.mpenv_map_nodes.restype = C.c_void_p
+    lib.mpenv_map_nodes.argtypes = [C.c_void_p]
+    lib.mpenv_map_verts.restype = C.c_void_p
+    lib.mpenv_map_verts.argtypes = [C.c_void_p]
+    lib.mpenv_map_free.argtypes = [C.c_void_p]
+    lib.mpenv_map_last_error.restype = C.c_char_p
+    m = C.c_void_p()
+    rc = lib.mpenv_map_load(scene.encode(), C.byref(m))
+    if rc != 0:
+        raise RuntimeError(f"mpenv_map_load failed ({rc}): {lib.mpenv_map_last_error().decode()}")
+    info = MapInfo()
+    lib.mpenv_map_info(m, C.byref(info))
+    nodes = np.ctypeslib.as_array(C.cast(lib.mpenv_map_nodes(m), C.POINTER(C.c_uint8)),
+                                  shape=(info.num_nodes, 64)).copy()
+    verts = np.ctypeslib.as_array(C.cast(lib.mpenv_map_verts(m), C.POINTER(C.c_float)),
+                                  shape=(info.num_tris * 3, 3)).copy()
+    lib.mpenv_map_free(m)
+    return nodes, verts, info
+
+
+# ------------------------------------------------------------------- oracle
+class RefConfig(C.Structure):
+    _fields_ = [("numWorlds", C.c_uint32), ("randSeed", C.c_uint32), ("autoReset", C.c_int32),
+                ("simFlags", C.c_uint32), ("taskType", C.c_uint32), ("teamSize", C.c_uint32),
+                ("numPBTPolicies", C.c_uint32), ("policyHistorySize", C.c_uint32),
+                ("worldIDOffset", C.c_uint32), ("numThreads", C.c_uint32)]
+
+
+class _SimBase:
+    num_worlds = 0
+
+    def export(self, name):
+        kind, cols, dt = EXPORT_SHAPES[name]
+        arr = np.empty((rows_of(kind, self.num_worlds), cols), dtype=dt)
+        self._read(EXPORT_IDS[name], arr)
+        return arr
+
+    def set_export(self, name, arr):
+        kind, cols, dt = EXPORT_SHAPES[name]
+        arr = np.ascontiguousarray(arr, dtype=dt).reshape(rows_of(kind, self.num_worlds), cols)
+        self._write(EXPORT_IDS[name], arr)
+
+    def set_actions(self, discrete, discrete_aim, aim=None):
+        self.set_export("pvp_discrete_action", discrete)
+        self.set_export("pvp_discrete_aim_action", discrete_aim)
+        if aim is not None:
+            self.set_export("pvp_aim_action", aim)
+
+    def world_state(self, w):
+        ws = WorldState()
+        self._state(w, ws)
+        return struct_to_dict(ws)
+
+
+class Oracle(_SimBase):
+    """The reference's own sim.cpp / utils.cpp / level_gen.cpp / mesh_bvh.inl under
+    oracle/shim.  det=True routes sinf/cosf/logf/atan2f/asinf to mp_math.h."""
+
+    def __init__(self, num_worlds, rand_seed=10, auto_reset=False, sim_flags=0, det=True,
+                 world_id_offset=0, num_threads=1, scene=SCENE, bvh=None):
+        build_oracle()
+        self.lib = C.CDLL(REF_DET_SO if det else REF_SO)
+        L = self.lib
+        L.ref_create.restype = C.c_void_p
+        L.ref_create.argtypes = [C.POINTER(RefConfig), C.c_char_p, C.c_void_p, C.c_uint32,
+                                 C.c_void_p, C.c_uint32, C.c_uint32, C.c_void_p]
+        for f in ("ref_destroy", "ref_init", "ref_step"):
+            getattr(L, f).argtypes = [C.c_void_p]
+        L.ref_read_export.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint64]
+        L.ref_write_export.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint64]
+        L.ref_get_world_state.argtypes = [C.c_void_p, C.c_uint32, C.POINTER(WorldState)]
+        L.ref_trace_ray.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_float, C.c_void_p]
+        L.ref_trace_ray_brute.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.ref_sphere_cast.restype = C.c_float
+        L.ref_sphere_cast.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_float, C.c_void_p]
+        L.ref_sphere_cast_brute.restype = C.c_float
+        L.ref_sphere_cast_brute.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_float]
+        L.ref_set_sim_control.argtypes = [C.c_void_p, C.c_void_p]
+        L.ref_num_threads.restype = C.c_uint32
+        L.ref_num_threads.argtypes = [C.c_void_p]
+        if bvh is None:
+            bvh = load_map(C.CDLL(build_hostsim()), scene)
+        nodes, verts, info = bvh
+        v20 = np.zeros((verts.shape[0], 5), dtype=np.float32)     # BVHVertex {pos, uv}
+        v20[:, :3] = verts
+        cfg = RefConfig(num_worlds, rand_seed, int(auto_reset), sim_flags, 2, 6, 0, 1,
+                        world_id_offset, num_threads)
+        root = np.array(list(info.root_aabb), dtype=np.float32)
+        self.h = L.ref_create(C.byref(cfg), scene.encode(), nodes.ctypes.data, info.num_nodes,
+                              v20.ctypes.data, verts.shape[0], info.num_leaves, root.ctypes.data)
+        if not self.h:
+            raise RuntimeError("ref_create failed")
+        self.num_worlds = num_worlds
+
+    def close(self):
+        if self.h:
+            self.lib.ref_destroy(self.h)
+            self.h = None
+
+    def init(self):
+        self.lib.ref_init(self.h)
+
+    def step(self):
+        self.lib.ref_step(self.h)
+
+    def num_threads(self):
+        return self.lib.ref_num_threads(self.h)
+
+    def _read(self, eid, arr):
+        rc = self.lib.ref_read_export(self.h, eid, arr.ctypes.data, arr.nbytes)
+        assert rc == 0, f"ref_read_export({eid}) -> {rc}"
+
+    def _write(self, eid, arr):
+        rc = self.lib.ref_write_export(self.h, eid, arr.ctypes.data, arr.nbytes)
+        assert rc == 0, f"ref_write_export({eid}) -> {rc}"
+
+    def _state(self, w, ws):
+        assert self.lib.ref_get_world_state(self.h, w, C.byref(ws)) == 0
+
+    def set_sim_control(self, v):
+        a = np.asarray(v, dtype=np.int32)
+        self.lib.ref_set_sim_control(self.h, a.ctypes.data)
+
+    def trace_ray(self, o, d):
+        o = np.asarray(o, np.float32); d = np.asarray(d, np.float32)
+        t = C.c_float()
+        hit = self.lib.ref_trace_ray(self.h, o.ctypes.data, d.ctypes.data, np.float32(3.4028234663852886e38), C.byref(t))
+        return hit, t.value
+
+    def trace_ray_brute(self, o, d):
+        o = np.asarray(o, np.float32); d = np.asarray(d, np.float32)
+        t = C.c_float()
+        hit = self.lib.ref_trace_ray_brute(self.h, o.ctypes.data, d.ctypes.data, C.byref(t))
+        return hit, t.value
+
+    def sphere_cast(self, o, d, r=15.0):
+        o = np.asarray(o, np.float32); d = np.asarray(d, np.float32)
+        n = np.zeros(3, np.float32)
+        t = self.lib.ref_sphere_cast(self.h, o.ctypes.data, d.ctypes.data, r, n.ctypes.data)
+        return t, n
+
+    def sphere_cast_brute(self, o, d, r=15.0):
+        o = np.asarray(o, np.float32); d = np.asarray(d, np.float32)
+        return self.lib.ref_sphere_cast_brute(self.h, o.ctypes.data, d.ctypes.data, r)
+
+
+# ------------------------------------------------------------------ hostsim
+class HostSimConfig(C.Structure):
+    _fields_ = [("numWorlds", C.c_uint32), ("randSeed", C.c_uint32), ("autoReset", C.c_int32),
+                ("simFlags", C.c_uint32), ("worldIDOffset", C.c_uint32), ("enableFullTeam", C.c_uint32)]
+
+
+class HostSim(_SimBase):
+    """Device stage functions compiled for the host (tests only)."""
+
+    def __init__(self, num_worlds, rand_seed=10, auto_reset=False, sim_flags=0, world_id_offset=0,
+                 full_team=True, scene=SCENE):
+        self.lib = C.CDLL(build_hostsim())
+        L = self.lib
+        L.hostsim_create.restype = C.c_void_p
+        L.hostsim_create.argtypes = [C.POINTER(HostSimConfig), C.c_char_p]
+        for f in ("hostsim_destroy", "hostsim_init", "hostsim_step"):
+            getattr(L, f).argtypes = [C.c_void_p]
+        L.hostsim_read_export.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint64]
+        L.hostsim_write_export.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint64]
+        L.hostsim_get_world_state.argtypes = [C.c_void_p, C.c_uint32, C.POINTER(WorldState)]
+        L.hostsim_trace_ray.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.hostsim_sphere_cast.restype = C.c_float
+        L.hostsim_sphere_cast.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_float, C.c_void_p]
+        cfg = HostSimConfig(num_worlds, rand_seed, int(auto_reset), sim_flags, world_id_offset,
+                            int(full_team))
+        self.h = L.hostsim_create(C.byref(cfg), scene.encode())
+        if not self.h:
+            raise RuntimeError("hostsim_create failed")
+        self.num_worlds = num_worlds
+
+    def close(self):
+        if self.h:
+            self.lib.hostsim_destroy(self.h)
+            self.h = None
+
+    def init(self):
+        self.lib.hostsim_init(self.h)
+
+    def step(self):
+        self.lib.hostsim_step(self.h)
+
+    def _read(self, eid, arr):
+        rc = self.lib.hostsim_read_export(self.h, eid, arr.ctypes.data, arr.nbytes)
+        assert rc == 0, f"hostsim_read_export({eid}) -> {rc}"
+
+    def _write(self, eid, arr):
+        rc = self.lib.hostsim_write_export(self.h, eid, arr.ctypes.data, arr.nbytes)
+        assert rc == 0, f"hostsim_write_export({eid}) -> {rc}"
+
+    def _state(self, w, ws):
+        assert self.lib.hostsim_get_world_state(self.h, w, C.byref(ws)) == 0
+
+    def trace_ray(self, o, d):
+        o = np.asarray(o, np.float32); d = np.asarray(d, np.float32)
+        t = C.c_float()
+        hit = self.lib.hostsim_trace_ray(self.h, o.ctypes.data, d.ctypes.data, C.byref(t))
+        return hit, t.value
+
+    def sphere_cast(self, o, d, r=15.0):
+        o = np.asarray(o, np.float32); d = np.asarray(d, np.float32)
+        n = np.zeros(3, np.float32)
+        t = self.lib.hostsim_sphere_cast(self.h, o.ctypes.data, d.ctypes.data, r, n.ctypes.data)
+        return t, n
+
+
+# ------------------------------------------------------------------ actions
+_ROT = (13, 15, 26, 6, 17, 29, 16, 24)
+
+
+def threefry_split(a, b, idx, idx_upper=0):
+    """Vectorised Threefry2x32-20 key split (same scheme as mp_math.h randSplit)."""
+    a = np.asarray(a, np.uint32); b = np.asarray(b, np.uint32)
+    ks = [a, b, np.uint32(0x1BD11BDA) ^ a ^ b]
+    with np.errstate(over="ignore"):
+        x0 = np.asarray(idx, np.uint32) + ks[0]
+        x1 = np.asarray(idx_upper, np.uint32) + ks[1]
+
+        def rounds(x0, x1, rs):
+            for r in rs:
+                x0 = x0 + x1
+                x1 = (x1 << np.uint32(r)) | (x1 >> np.uint32(32 - r))
+                x1 = x1 ^ x0
+            return x0, x1
+        x0, x1 = rounds(x0, x1, _ROT[:4]); x0 = x0 + ks[1]; x1 = x1 + ks[2] + np.uint32(1)
+        x0, x1 = rounds(x0, x1, _ROT[4:]); x0 = x0 + ks[2]; x1 = x1 + ks[0] + np.uint32(2)
+        x0, x1 = rounds(x0, x1, _ROT[:4]); x0 = x0 + ks[0]; x1 = x1 + ks[1] + np.uint32(3)
+        x0, x1 = rounds(x0, x1, _ROT[4:]); x0 = x0 + ks[1]; x1 = x1 + ks[2] + np.uint32(4)
+        x0, x1 = rounds(x0, x1, _ROT[:4])
+        return x0 + ks[2], x1 + ks[0] + np.uint32(5)
+
+
+def random_actions(step, num_worlds, world_id_offset=0, seed=1234, stress=False, magazine=None):
+    """The synthetic action stream of SURVEY 8(d): a counter RNG keyed on (seed,
+    step, global_world*12+agent), so every shard / implementation consumes the
+    same stream.  Returns (discrete i32[N,4], discrete_aim i32[N,2])."""
+    n = num_worlds * AGENTS
+    gid = (np.arange(n, dtype=np.uint64) + np.uint64(world_id_offset) * np.uint64(AGENTS)).astype(np.uint32)
+    k0, k1 = threefry_split(np.uint32(seed), np.uint32(0x9E3779B9), gid, np.uint32(step))
+    r0, r1 = threefry_split(k0, k1, np.uint32(0))
+    r2, r3 = threefry_split(k0, k1, np.uint32(1))
+    u = lambda bits: (bits >> np.uint32(8)).astype(np.float32) * np.float32(2.0 ** -24)
+    move_amount = (r0 % np.uint32(3)).astype(np.int32)
+    move_angle = ((r0 >> np.uint32(8)) % np.uint32(8)).astype(np.int32)
+    uf = u(r1)
+    fire = np.where(uf < 0.6, 0, np.where(uf < 0.95, 1, 2)).astype(np.int32)
+    us = u(r2)
+    stand = np.where(us < 0.8, 0, np.where(us < 0.9, 1, 2)).astype(np.int32)
+    yaw = (r3 % np.uint32(13)).astype(np.int32)
+    pitch = ((r3 >> np.uint32(8)) % np.uint32(7)).astype(np.int32)
+    if stress:
+        fire = np.ones(n, np.int32)
+        if magazine is not None:
+            fire = np.where(np.asarray(magazine).reshape(n, 2)[:, 0] == 0, 2, 1).astype(np.int32)
+    discrete = np.stack([move_amount, move_angle, fire, stand], axis=1)
+    discrete_aim = np.stack([yaw, pitch], axis=1)
+    return discrete, discrete_aim
