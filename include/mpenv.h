@@ -133,6 +133,16 @@ int mpenv_sync(mpenv_handle *h);
 /* Manager::*Tensor() exporters (mgr.cpp:1965-2381). */
 int mpenv_tensor(mpenv_handle *h, uint32_t export_id, mpenv_tensor_desc *out);
 
+/* Host-buffer access to a tensor: the copies cudaCopyStepInputs /
+ * cudaCopyStepOutputs and the viewer setters do (mgr.cpp:625-629, 2492-2565),
+ * for callers that hold HOST memory.  Stream-ordered on the handle's stream
+ * (follow with mpenv_sync); `bytes` must equal the tensor's size.  Pinned host
+ * memory from mpenv_host_alloc makes the copies truly asynchronous. */
+int mpenv_write_tensor_async(mpenv_handle *h, uint32_t export_id, const void *host_src, uint64_t bytes);
+int mpenv_read_tensor_async(mpenv_handle *h, uint32_t export_id, void *host_dst, uint64_t bytes);
+int mpenv_host_alloc(uint64_t bytes, void **out);
+void mpenv_host_free(void *p);
+
 /* Manager::trainInterface (mgr.cpp:2383-2431): the named input / output tensors
  * in the order the stream entry points expect their buffers. */
 typedef struct mpenv_named_tensor {

@@ -206,7 +206,7 @@ MP_HD void zoneFrame(const MapConsts &mc, int32_t zone, Quat *to_zone, AABB *box
 }
 
 // spawnAgents (utils.cpp:734-948) for the supported flag set (standard spawns;
-// RandomizeHPMagazine honoured; NavmeshSpawn / HardcodedSpawns / SpawnInMiddle
+// RandomizeHPMagazine and the LearnShooting curriculum spawn honoured; NavmeshSpawn / HardcodedSpawns / SpawnInMiddle
 // / curriculum spawns are rejected at create time).
 MP_HD void spawnAgents(const Ctx &c, int w, bool is_respawn)
 {
@@ -229,6 +229,14 @@ MP_HD void spawnAgents(const Ctx &c, int w, bool is_respawn)
         float spawn_yaw;
         const float spawn_pitch = 0.f;
         standardSpawnPoint(c, w, a, is_respawn, &spawn_pt, &spawn_yaw);
+        if ((c.cfg.simFlags & kFlagEnableCurriculum) && p.world[w].episodeCurriculum == 0) {
+            // LearnShooting curriculum (utils.cpp:819-837): re-draw the point in
+            // the half of the arena the standard spawn fell in.
+            float rx = rngUniform(base_rng);
+            float ry = rngUniform(base_rng);
+            if (spawn_pt.y > 0.f) spawn_pt = v3(-700.f + rx * 1400.f, ry * 350.f, 0.f);
+            else spawn_pt = v3(-700.f + rx * 1400.f, -ry * 350.f, 0.f);
+        }
 
         p.pos[idx] = spawn_pt;
         p.rot[idx] = quatNormalize(angleAxis(spawn_yaw, kUp()));

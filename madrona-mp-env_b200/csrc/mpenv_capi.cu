@@ -1,0 +1,526 @@
+// mpenv_capi.cu -- the C ABI of libmpenv_b200.so (include/mpenv.h): device
+// state ownership, kernel launch sequence, CUDA-graph capture of the step, and
+// the tensor table.  Replaces Manager::Impl / CUDAImpl of the reference
+// (src/mgr.cpp:305-662, 1213-1912) for the per-step simulation path.
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "step_kernels.cuh"
+#include "assets.h"
+#include "sim_layout.h"
+#include "../../include/mpenv.h"
+
+using namespace mpenv;
+
+namespace mpenv {
+const MapAssets &mapAssetsOf(const mpenv_map *m);
+}
+
+static thread_local std::string g_create_error;
+
+struct mpenv_handle {
+    mpenv_config cfg;
+    std::string sceneDir;
+    std::string error;
+    int device = 0;
+    int numSMs = 0;
+    cudaStream_t stream = nullptr;
+    MapAssets assets;
+    MapConsts hostConsts;
+    MapConsts *devConsts = nullptr;
+    BVHNode *devNodes = nullptr;
+    Vec3 *devVerts = nullptr;
+    KernelArgs ka;
+    std::vector<void *> allocs;
+    float *agentMap = nullptr;               // [N,16,16,4] zeros (never written, mgr.cpp:2422)
+    unsigned long long *devStats = nullptr;
+    size_t bvhSmemBytes = 0;
+    cudaGraphExec_t stepGraph = nullptr;
+    cudaGraphExec_t initGraph = nullptr;
+    bool fullTeam = false;
+    // launch geometry
+    int gridMove = 0, gridFire = 0, gridWorld = 0, gridLos = 0, gridObs = 0, gridTeam = 0, gridLidar = 0,
+        gridSmall = 0;
+    uint32_t stepLaunches = 0, initLaunches = 0;
+};
+
+namespace {
+
+bool cudaOk(mpenv_handle *h, cudaError_t e, const char *what)
+{
+    if (e == cudaSuccess) return true;
+    char buf[512];
+    snprintf(buf, sizeof(buf), "%s: %s", what, cudaGetErrorString(e));
+    if (h) h->error = buf;
+    g_create_error = buf;
+    return false;
+}
+
+#define MP_CUDA(h, call) do { if (!cudaOk((h), (call), #call)) return MPENV_ERR_CUDA; } while (0)
+
+int fail(mpenv_handle *h, int code, const std::string &msg)
+{
+    if (h) h->error = msg;
+    g_create_error = msg;
+    return code;
+}
+
+template <typename K>
+int gridFor(mpenv_handle *h, K kernel, int block, size_t smem, long long items)
+{
+    int per_sm = 1;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, block, smem) != cudaSuccess || per_sm < 1)
+        per_sm = 1;
+    long long want = (items + block - 1) / block;
+    long long cap = (long long)h->numSMs * per_sm;
+    if (want < 1) want = 1;
+    return (int)(want < cap ? want : cap);
+}
+
+// The obs phase shared by the Init and Step graphs (resetAndObsTasks,
+// sim.cpp:5174-5320): visibility -> masks + observations -> full-team -> lidar.
+uint32_t launchObsPhase(mpenv_handle *h, cudaStream_t s)
+{
+    uint32_t n = 0;
+    k_los<<<h->gridLos, 128, h->bvhSmemBytes, s>>>(h->ka); n++;
+    k_obs<<<h->gridObs, 128, 0, s>>>(h->ka); n++;
+    if (h->fullTeam) { k_fullteam<<<h->gridTeam, 128, 0, s>>>(h->ka); n++; }
+    k_lidar<<<h->gridLidar, 160, h->bvhSmemBytes, s>>>(h->ka); n++;
+    return n;
+}
+
+uint32_t launchStep(mpenv_handle *h, cudaStream_t s)
+{
+    uint32_t n = 0;
+    k_move<<<h->gridMove, 128, h->bvhSmemBytes, s>>>(h->ka); n++;
+    k_fire<<<h->gridFire, 128, h->bvhSmemBytes, s>>>(h->ka); n++;
+    k_world<<<h->gridWorld, 64, 0, s>>>(h->ka); n++;
+    n += launchObsPhase(h, s);
+    return n;
+}
+
+uint32_t launchInit(mpenv_handle *h, cudaStream_t s)
+{
+    uint32_t n = 0;
+    k_force_reset<<<h->gridSmall, 128, 0, s>>>(h->ka); n++;
+    k_reset<<<h->gridSmall, 128, 0, s>>>(h->ka); n++;
+    n += launchObsPhase(h, s);
+    return n;
+}
+
+int captureGraph(mpenv_handle *h, bool step, cudaGraphExec_t *out, uint32_t *launches)
+{
+    cudaGraph_t graph = nullptr;
+    MP_CUDA(h, cudaStreamBeginCapture(h->stream, cudaStreamCaptureModeThreadLocal));
+    *launches = step ? launchStep(h, h->stream) : launchInit(h, h->stream);
+    MP_CUDA(h, cudaStreamEndCapture(h->stream, &graph));
+    MP_CUDA(h, cudaGraphInstantiate(out, graph, 0));
+    MP_CUDA(h, cudaGraphDestroy(graph));
+    return MPENV_OK;
+}
+
+const mpenv_named_tensor kTrainInterface[] = {
+    // inputs (mgr.cpp:2386-2396)
+    { "discrete", MPENV_EXPORT_PVP_DISCRETE_ACTION, 1 },
+    { "aim", MPENV_EXPORT_PVP_DISCRETE_AIM_ACTION, 1 },
+    { "resets", MPENV_EXPORT_RESET, 1 },
+    { "sim_ctrl", MPENV_EXPORT_SIM_CONTROL, 1 },
+    { "policy_assignments", MPENV_EXPORT_AGENT_POLICY, 1 },
+    // outputs (mgr.cpp:2398-2430)
+    { "fwd_lidar", MPENV_EXPORT_FWD_LIDAR, 0 },
+    { "rear_lidar", MPENV_EXPORT_REAR_LIDAR, 0 },
+    { "hp", MPENV_EXPORT_HP, 0 },
+    { "magazine", MPENV_EXPORT_MAGAZINE, 0 },
+    { "alive", MPENV_EXPORT_ALIVE, 0 },
+    { "self", MPENV_EXPORT_SELF_OBSERVATION, 0 },
+    { "filters_state", MPENV_EXPORT_FILTERS_STATE_OBSERVATION, 0 },
+    { "teammates", MPENV_EXPORT_TEAMMATE_OBSERVATIONS, 0 },
+    { "opponents", MPENV_EXPORT_OPPONENT_OBSERVATIONS, 0 },
+    { "opponents_last_known", MPENV_EXPORT_OPPONENT_LAST_KNOWN_OBSERVATIONS, 0 },
+    { "self_pos", MPENV_EXPORT_SELF_POSITION_OBSERVATION, 0 },
+    { "teammate_positions", MPENV_EXPORT_TEAMMATE_POSITION_OBSERVATIONS, 0 },
+    { "opponent_positions", MPENV_EXPORT_OPPONENT_POSITION_OBSERVATIONS, 0 },
+    { "opponent_last_known_positions", MPENV_EXPORT_OPPONENT_LAST_KNOWN_POSITION_OBSERVATIONS, 0 },
+    { "opponent_masks", MPENV_EXPORT_OPPONENT_MASKS, 0 },
+    { "agent_map", MPENV_EXPORT_AGENT_MAP, 0 },
+    { "unmasked_agent_map", MPENV_EXPORT_AGENT_MAP, 0 },     // bound to agentMapTensor (mgr.cpp:2422)
+    { "reward_coefs", MPENV_EXPORT_REWARD_HYPER_PARAMS, 0 },
+    { "rewards", MPENV_EXPORT_REWARD, 0 },
+    { "dones", MPENV_EXPORT_DONE, 0 },
+    { "episode_results", MPENV_EXPORT_MATCH_RESULT, 0 },
+};
+constexpr uint32_t kNumTrainTensors = sizeof(kTrainInterface) / sizeof(kTrainInterface[0]);
+
+size_t tensorBytes(const mpenv_tensor_desc &d)
+{
+    size_t n = 4;
+    for (int i = 0; i < d.ndim; i++) n *= (size_t)d.dims[i];
+    return n;
+}
+
+int copyInterface(mpenv_handle *h, cudaStream_t s, void **buffers, bool inputs)
+{
+    for (uint32_t i = 0; i < kNumTrainTensors; i++) {
+        if ((kTrainInterface[i].is_input != 0) != inputs) continue;
+        if (!buffers[i]) continue;          // NULL = caller aliases the sim tensor directly
+        mpenv_tensor_desc d;
+        int rc = mpenv_tensor(h, kTrainInterface[i].export_id, &d);
+        if (rc != MPENV_OK) return rc;
+        if (buffers[i] == d.dev_ptr) continue;
+        if (inputs) MP_CUDA(h, cudaMemcpyAsync(d.dev_ptr, buffers[i], tensorBytes(d), cudaMemcpyDeviceToDevice, s));
+        else MP_CUDA(h, cudaMemcpyAsync(buffers[i], d.dev_ptr, tensorBytes(d), cudaMemcpyDeviceToDevice, s));
+    }
+    return MPENV_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+const char *mpenv_last_error(mpenv_handle *h) { return h ? h->error.c_str() : g_create_error.c_str(); }
+
+void mpenv_destroy(mpenv_handle *h)
+{
+    if (!h) return;
+    cudaSetDevice(h->device);
+    if (h->stream) cudaStreamSynchronize(h->stream);
+    if (h->stepGraph) cudaGraphExecDestroy(h->stepGraph);
+    if (h->initGraph) cudaGraphExecDestroy(h->initGraph);
+    for (void *p : h->allocs) cudaFree(p);
+    if (h->stream) cudaStreamDestroy(h->stream);
+    delete h;
+}
+
+int mpenv_create(const mpenv_config *cfg, mpenv_handle **out)
+{
+    if (!cfg || !out || !cfg->scene_dir) return fail(nullptr, MPENV_ERR_INVALID, "null argument");
+    if (cfg->task_type != MPENV_TASK_ZONE) return fail(nullptr, MPENV_ERR_INVALID, "only Task::Zone is implemented");
+    if (cfg->team_size != (uint32_t)kTeamSize) return fail(nullptr, MPENV_ERR_INVALID, "team_size must be 6");
+    if (cfg->num_worlds == 0 || cfg->num_worlds > (1u << 22)) return fail(nullptr, MPENV_ERR_INVALID, "num_worlds out of range");
+    const uint32_t unsupported = MPENV_FLAG_SPAWN_IN_MIDDLE | MPENV_FLAG_NAVMESH_SPAWN |
+        MPENV_FLAG_HARDCODED_SPAWNS | MPENV_FLAG_FULL_TEAM_POLICY | MPENV_FLAG_SUBZONES;
+    if (cfg->sim_flags & unsupported) return fail(nullptr, MPENV_ERR_INVALID, "unsupported sim_flags bit set");
+
+    int dev_count = 0;
+    cudaError_t e = cudaGetDeviceCount(&dev_count);
+    if (e != cudaSuccess || dev_count == 0) {
+        return fail(nullptr, MPENV_ERR_CUDA, std::string("no usable CUDA device: ") + cudaGetErrorString(e) +
+                    " (libmpenv_b200 has no CPU execution path)");
+    }
+    if (cfg->gpu_id < 0 || cfg->gpu_id >= dev_count) return fail(nullptr, MPENV_ERR_INVALID, "gpu_id out of range");
+
+    mpenv_handle *h = new mpenv_handle();
+    h->cfg = *cfg;
+    h->sceneDir = cfg->scene_dir;
+    h->cfg.scene_dir = h->sceneDir.c_str();
+    h->device = cfg->gpu_id;
+    h->fullTeam = cfg->enable_full_team != 0;
+    auto bail = [&](int code) { std::string m = h->error; mpenv_destroy(h); g_create_error = m; return code; };
+
+    std::string err;
+    if (!loadMapAssets(h->sceneDir, &h->assets, &err) || !fillMapConsts(h->assets, &h->hostConsts, &err)) {
+        h->error = err;
+        return bail(MPENV_ERR_IO);
+    }
+
+#define MP_CREATE(call) do { if (!cudaOk(h, (call), #call)) return bail(MPENV_ERR_CUDA); } while (0)
+    MP_CREATE(cudaSetDevice(h->device));
+    cudaDeviceProp prop;
+    MP_CREATE(cudaGetDeviceProperties(&prop, h->device));
+    h->numSMs = prop.multiProcessorCount;
+    MP_CREATE(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
+
+    auto devAlloc = [&](void **ptr, size_t bytes) -> bool {
+        if (!cudaOk(h, cudaMalloc(ptr, bytes), "cudaMalloc")) return false;
+        h->allocs.push_back(*ptr);
+        return cudaOk(h, cudaMemsetAsync(*ptr, 0, bytes, h->stream), "cudaMemsetAsync");
+    };
+
+    // static assets
+    const size_t node_bytes = h->assets.nodes.size() * sizeof(BVHNode);
+    const size_t vert_bytes = h->assets.verts.size() * sizeof(Vec3);
+    if (!devAlloc((void **)&h->devNodes, node_bytes) || !devAlloc((void **)&h->devVerts, vert_bytes + 16) ||
+        !devAlloc((void **)&h->devConsts, sizeof(MapConsts)))
+        return bail(MPENV_ERR_CUDA);
+    MP_CREATE(cudaMemcpyAsync(h->devNodes, h->assets.nodes.data(), node_bytes, cudaMemcpyHostToDevice, h->stream));
+    MP_CREATE(cudaMemcpyAsync(h->devVerts, h->assets.verts.data(), vert_bytes, cudaMemcpyHostToDevice, h->stream));
+    MP_CREATE(cudaMemcpyAsync(h->devConsts, &h->hostConsts, sizeof(MapConsts), cudaMemcpyHostToDevice, h->stream));
+
+    // state + export buffers
+    KernelArgs &ka = h->ka;
+    memset(&ka, 0, sizeof(ka));
+    int nbuf;
+    const BufferDesc *table = bufferTable(&nbuf);
+    for (int i = 0; i < nbuf; i++) {
+        size_t bytes = bufferRows(table[i], cfg->num_worlds) * table[i].rowBytes;
+        if (!devAlloc(bufferSlot(&ka.ctx.p, table[i]), bytes)) return bail(MPENV_ERR_CUDA);
+    }
+    if (!devAlloc((void **)&h->devStats, sizeof(unsigned long long) * MPENV_NUM_STATS)) return bail(MPENV_ERR_CUDA);
+
+    ka.ctx.cfg.numWorlds = cfg->num_worlds;
+    ka.ctx.cfg.worldIDOffset = cfg->world_id_offset;
+    ka.ctx.cfg.simFlags = cfg->sim_flags;
+    ka.ctx.cfg.autoReset = cfg->auto_reset;
+    ka.ctx.cfg.initRandKey = randSplit(randInitKey(cfg->rand_seed), 0);     // mgr.cpp:1736-1738
+    ka.ctx.mc = h->devConsts;
+    ka.ctx.bvh.nodes = h->devNodes;
+    ka.ctx.bvh.verts = h->devVerts;
+    ka.ctx.bvh.rootAABB = h->assets.rootAABB;
+    ka.ctx.bvh.numNodes = (uint32_t)h->assets.nodes.size();
+    ka.ctx.bvh.numTris = h->assets.numTris;
+    ka.bvhNodeWords = (uint32_t)(node_bytes / 4);
+    ka.bvhVertWords = (uint32_t)(vert_bytes / 4);
+    h->bvhSmemBytes = node_bytes + ((vert_bytes + 15) / 16) * 16;
+    ka.bvhInSmem = h->bvhSmemBytes <= 160 * 1024 ? 1 : 0;
+    if (!ka.bvhInSmem) h->bvhSmemBytes = 0;
+
+    // TrainControl from the flags (mgr.cpp:1397-1413)
+    TrainControl tc;
+    tc.evalMode = (cfg->sim_flags & MPENV_FLAG_SIM_EVAL_MODE) ? 1 : 0;
+    tc.randomizeEpisodeLengthAfterReset = (cfg->sim_flags & MPENV_FLAG_STAGGER_STARTS) ? 1 : 0;
+    tc.randomizeTeamSides = (cfg->sim_flags & MPENV_FLAG_RANDOM_FLIP_TEAMS) ? 1 : 0;
+    MP_CREATE(cudaMemcpyAsync(ka.ctx.p.trainCtrl, &tc, sizeof(tc), cudaMemcpyHostToDevice, h->stream));
+
+    if (h->bvhSmemBytes > 48 * 1024) {
+        MP_CREATE(cudaFuncSetAttribute(k_move, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->bvhSmemBytes));
+        MP_CREATE(cudaFuncSetAttribute(k_fire, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->bvhSmemBytes));
+        MP_CREATE(cudaFuncSetAttribute(k_los, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->bvhSmemBytes));
+        MP_CREATE(cudaFuncSetAttribute(k_lidar, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->bvhSmemBytes));
+    }
+
+    const long long W = cfg->num_worlds, N = W * kAgents;
+    h->gridMove = gridFor(h, k_move, 128, h->bvhSmemBytes, N);
+    h->gridFire = gridFor(h, k_fire, 128, h->bvhSmemBytes, N);
+    h->gridWorld = gridFor(h, k_world, 64, 0, W);
+    h->gridLos = gridFor(h, k_los, 128, h->bvhSmemBytes, N * kTeamSize);
+    h->gridObs = gridFor(h, k_obs, 128, 0, N);
+    h->gridTeam = gridFor(h, k_fullteam, 128, 0, W * 2);
+    h->gridLidar = gridFor(h, k_lidar, 160, h->bvhSmemBytes, N * 80);
+    h->gridSmall = gridFor(h, k_reset, 128, 0, W);
+
+    // Sim::Sim for every world (sim.cpp:5850-5980)
+    k_ctor<<<h->gridSmall, 128, 0, h->stream>>>(ka);
+    MP_CREATE(cudaGetLastError());
+    MP_CREATE(cudaStreamSynchronize(h->stream));
+
+    if (captureGraph(h, true, &h->stepGraph, &h->stepLaunches) != MPENV_OK ||
+        captureGraph(h, false, &h->initGraph, &h->initLaunches) != MPENV_OK)
+        return bail(MPENV_ERR_CUDA);
+#undef MP_CREATE
+    *out = h;
+    return MPENV_OK;
+}
+
+int mpenv_init_async(mpenv_handle *h, void *cuda_stream)
+{
+    if (!h) return MPENV_ERR_INVALID;
+    MP_CUDA(h, cudaSetDevice(h->device));
+    MP_CUDA(h, cudaGraphLaunch(h->initGraph, (cudaStream_t)cuda_stream));
+    return MPENV_OK;
+}
+
+int mpenv_step_async(mpenv_handle *h, void *cuda_stream)
+{
+    if (!h) return MPENV_ERR_INVALID;
+    MP_CUDA(h, cudaSetDevice(h->device));
+    MP_CUDA(h, cudaGraphLaunch(h->stepGraph, (cudaStream_t)cuda_stream));
+    return MPENV_OK;
+}
+
+int mpenv_sync(mpenv_handle *h)
+{
+    if (!h) return MPENV_ERR_INVALID;
+    MP_CUDA(h, cudaSetDevice(h->device));
+    MP_CUDA(h, cudaStreamSynchronize(h->stream));
+    return MPENV_OK;
+}
+
+int mpenv_init(mpenv_handle *h)
+{
+    int rc = mpenv_init_async(h, h ? h->stream : nullptr);
+    return rc != MPENV_OK ? rc : mpenv_sync(h);
+}
+
+int mpenv_step(mpenv_handle *h)
+{
+    int rc = mpenv_step_async(h, h ? h->stream : nullptr);
+    return rc != MPENV_OK ? rc : mpenv_sync(h);
+}
+
+int mpenv_stream_init(mpenv_handle *h, void *cuda_stream, void **buffers)
+{
+    if (!h || !buffers) return MPENV_ERR_INVALID;
+    int rc = mpenv_init_async(h, cuda_stream);
+    if (rc != MPENV_OK) return rc;
+    return copyInterface(h, (cudaStream_t)cuda_stream, buffers, false);
+}
+
+int mpenv_stream_step(mpenv_handle *h, void *cuda_stream, void **buffers)
+{
+    if (!h || !buffers) return MPENV_ERR_INVALID;
+    MP_CUDA(h, cudaSetDevice(h->device));
+    int rc = copyInterface(h, (cudaStream_t)cuda_stream, buffers, true);
+    if (rc != MPENV_OK) return rc;
+    rc = mpenv_step_async(h, cuda_stream);
+    if (rc != MPENV_OK) return rc;
+    return copyInterface(h, (cudaStream_t)cuda_stream, buffers, false);
+}
+
+int mpenv_tensor(mpenv_handle *h, uint32_t export_id, mpenv_tensor_desc *out)
+{
+    if (!h || !out) return MPENV_ERR_INVALID;
+    ExportDesc d;
+    if (export_id == MPENV_EXPORT_AGENT_MAP || export_id == MPENV_EXPORT_UNMASKED_AGENT_MAP) {
+        if (!h->agentMap) {
+            MP_CUDA(h, cudaSetDevice(h->device));
+            size_t bytes = (size_t)h->cfg.num_worlds * kAgents * 16 * 16 * 4 * sizeof(float);
+            MP_CUDA(h, cudaMalloc((void **)&h->agentMap, bytes));
+            h->allocs.push_back(h->agentMap);
+            MP_CUDA(h, cudaMemset(h->agentMap, 0, bytes));
+        }
+        out->dev_ptr = h->agentMap; out->dtype = MPENV_DTYPE_F32; out->ndim = 4;
+        out->dims[0] = (int64_t)h->cfg.num_worlds * kAgents; out->dims[1] = 16; out->dims[2] = 16; out->dims[3] = 4;
+        out->gpu_id = h->device;
+        return MPENV_OK;
+    }
+    if (!exportDesc(h->ka.ctx.p, h->cfg.num_worlds, export_id, &d)) {
+        return fail(h, MPENV_ERR_INVALID, "tensor not exported by this build (export id " + std::to_string(export_id) + ")");
+    }
+    out->dev_ptr = d.ptr; out->dtype = d.dtype; out->ndim = d.ndim;
+    for (int i = 0; i < 4; i++) out->dims[i] = d.dims[i];
+    if (export_id == MPENV_EXPORT_SIM_CONTROL) { out->ndim = 1; out->dims[0] = 3; out->dims[1] = 0; }
+    out->gpu_id = h->device;
+    return MPENV_OK;
+}
+
+int mpenv_write_tensor_async(mpenv_handle *h, uint32_t export_id, const void *host_src, uint64_t bytes)
+{
+    if (!h || !host_src) return MPENV_ERR_INVALID;
+    mpenv_tensor_desc d;
+    int rc = mpenv_tensor(h, export_id, &d);
+    if (rc != MPENV_OK) return rc;
+    if (bytes != tensorBytes(d)) return fail(h, MPENV_ERR_INVALID, "mpenv_write_tensor_async: size mismatch");
+    MP_CUDA(h, cudaSetDevice(h->device));
+    MP_CUDA(h, cudaMemcpyAsync(d.dev_ptr, host_src, bytes, cudaMemcpyHostToDevice, h->stream));
+    return MPENV_OK;
+}
+
+int mpenv_read_tensor_async(mpenv_handle *h, uint32_t export_id, void *host_dst, uint64_t bytes)
+{
+    if (!h || !host_dst) return MPENV_ERR_INVALID;
+    mpenv_tensor_desc d;
+    int rc = mpenv_tensor(h, export_id, &d);
+    if (rc != MPENV_OK) return rc;
+    if (bytes != tensorBytes(d)) return fail(h, MPENV_ERR_INVALID, "mpenv_read_tensor_async: size mismatch");
+    MP_CUDA(h, cudaSetDevice(h->device));
+    MP_CUDA(h, cudaMemcpyAsync(host_dst, d.dev_ptr, bytes, cudaMemcpyDeviceToHost, h->stream));
+    return MPENV_OK;
+}
+
+int mpenv_host_alloc(uint64_t bytes, void **out)
+{
+    if (!out) return MPENV_ERR_INVALID;
+    if (!cudaOk(nullptr, cudaMallocHost(out, bytes), "cudaMallocHost")) return MPENV_ERR_CUDA;
+    return MPENV_OK;
+}
+
+void mpenv_host_free(void *p) { if (p) cudaFreeHost(p); }
+
+int mpenv_train_interface(mpenv_handle *h, const mpenv_named_tensor **out, uint32_t *count)
+{
+    if (!h || !out || !count) return MPENV_ERR_INVALID;
+    *out = kTrainInterface;
+    *count = kNumTrainTensors;
+    return MPENV_OK;
+}
+
+int mpenv_trigger_reset(mpenv_handle *h, int32_t world_idx)
+{
+    if (!h || world_idx < 0 || (uint32_t)world_idx >= h->cfg.num_worlds) return MPENV_ERR_INVALID;
+    MP_CUDA(h, cudaSetDevice(h->device));
+    int32_t one = 1;
+    MP_CUDA(h, cudaMemcpy(h->ka.ctx.p.resetFlag + world_idx, &one, 4, cudaMemcpyHostToDevice));
+    return MPENV_OK;
+}
+
+int mpenv_set_pvp_action(mpenv_handle *h, int32_t world_idx, int32_t agent_idx, const int32_t discrete[4],
+                         const float aim[2], const int32_t discrete_aim[2])
+{
+    if (!h || world_idx < 0 || (uint32_t)world_idx >= h->cfg.num_worlds || agent_idx < 0 || agent_idx >= kAgents)
+        return MPENV_ERR_INVALID;
+    MP_CUDA(h, cudaSetDevice(h->device));
+    const size_t idx = (size_t)world_idx * kAgents + agent_idx;
+    MP_CUDA(h, cudaMemcpy(h->ka.ctx.p.actDiscrete + idx, discrete, 16, cudaMemcpyHostToDevice));
+    MP_CUDA(h, cudaMemcpy(h->ka.ctx.p.actAim + idx, aim, 8, cudaMemcpyHostToDevice));
+    MP_CUDA(h, cudaMemcpy(h->ka.ctx.p.actDiscreteAim + idx, discrete_aim, 8, cudaMemcpyHostToDevice));
+    return MPENV_OK;
+}
+
+int mpenv_set_hp(mpenv_handle *h, int32_t world_idx, int32_t agent_idx, int32_t hp)
+{
+    if (!h || world_idx < 0 || (uint32_t)world_idx >= h->cfg.num_worlds || agent_idx < 0 || agent_idx >= kAgents)
+        return MPENV_ERR_INVALID;
+    MP_CUDA(h, cudaSetDevice(h->device));
+    float v = (float)hp;
+    MP_CUDA(h, cudaMemcpy(h->ka.ctx.p.hp + (size_t)world_idx * kAgents + agent_idx, &v, 4, cudaMemcpyHostToDevice));
+    return MPENV_OK;
+}
+
+int mpenv_set_uniform_agent_policy(mpenv_handle *h, int32_t policy_idx)
+{
+    if (!h) return MPENV_ERR_INVALID;
+    MP_CUDA(h, cudaSetDevice(h->device));
+    std::vector<int32_t> v((size_t)h->cfg.num_worlds * kAgents, policy_idx);
+    MP_CUDA(h, cudaMemcpy(h->ka.ctx.p.policy, v.data(), v.size() * 4, cudaMemcpyHostToDevice));
+    return MPENV_OK;
+}
+
+int mpenv_episode_stats_async(mpenv_handle *h, void *cuda_stream, int64_t **dev_out)
+{
+    if (!h || !dev_out) return MPENV_ERR_INVALID;
+    MP_CUDA(h, cudaSetDevice(h->device));
+    cudaStream_t s = (cudaStream_t)cuda_stream;
+    MP_CUDA(h, cudaMemsetAsync(h->devStats, 0, sizeof(unsigned long long) * MPENV_NUM_STATS, s));
+    int grid = (int)((h->cfg.num_worlds + 255) / 256);
+    if (grid > h->numSMs * 4) grid = h->numSMs * 4;
+    k_stats<<<grid, 256, 0, s>>>(h->ka, h->devStats);
+    MP_CUDA(h, cudaGetLastError());
+    *dev_out = (int64_t *)h->devStats;
+    return MPENV_OK;
+}
+
+int mpenv_get_world_state(mpenv_handle *h, uint32_t world_idx, mpenv_world_state *out)
+{
+    if (!h || !out || world_idx >= h->cfg.num_worlds) return MPENV_ERR_INVALID;
+    MP_CUDA(h, cudaSetDevice(h->device));
+    MP_CUDA(h, cudaStreamSynchronize(h->stream));
+    int nbuf;
+    const BufferDesc *table = bufferTable(&nbuf);
+    SimPtrs one;
+    memset(&one, 0, sizeof(one));
+    std::vector<std::vector<char>> staging(nbuf);
+    for (int i = 0; i < nbuf; i++) {
+        if (table[i].kind == kGlobal) continue;
+        if (strcmp(table[i].name, "exploreGrid") == 0) continue;     // 26 KB / agent, not inspected
+        size_t rows = table[i].kind == kPerAgent ? kAgents : (table[i].kind == kPerTeam ? 2 : 1);
+        size_t bytes = rows * table[i].rowBytes;
+        staging[i].resize(bytes);
+        const char *src = (const char *)*bufferSlot(&h->ka.ctx.p, table[i]) + (size_t)world_idx * bytes;
+        MP_CUDA(h, cudaMemcpy(staging[i].data(), src, bytes, cudaMemcpyDeviceToHost));
+        *bufferSlot(&one, table[i]) = staging[i].data();
+    }
+    fillWorldState(one, out);
+    return MPENV_OK;
+}
+
+int mpenv_launches_per_step(mpenv_handle *h, uint32_t *step_launches, uint32_t *init_launches)
+{
+    if (!h) return MPENV_ERR_INVALID;
+    if (step_launches) *step_launches = h->stepLaunches;
+    if (init_launches) *init_launches = h->initLaunches;
+    return MPENV_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,192 @@
+// step_kernels.cuh -- the sm_100a kernels of one MadronaMPEnv step, one per
+// stage group of the reference Step task graph (sim.cpp:5342-5842):
+//
+//   k_move      movement + aim + swept-sphere collision + fall   (thread / agent)
+//   k_fire      hitscan fire                                     (thread / agent)
+//   k_world     damage, respawn, zone, breadcrumbs, match info,
+//               rewards, done, reset                             (thread / world)
+//   k_los       line-of-sight visibility                         (thread / (agent, opponent))
+//   k_obs       opponent masks + observation packing             (thread / agent)
+//   k_fullteam  full-team observation tensors (optional)         (warp / team)
+//   k_lidar     80 lidar rays per agent                          (thread / ray)
+//
+// All kernels are persistent grid-stride loops sized from the SM count; the
+// static-mesh BVH (nodes + de-indexed triangle positions, ~13 KB on
+// simple_map) is staged into shared memory once per CTA, so traversal never
+// touches global memory; world state is read / written with plain coalesced
+// loads and stores.  Compiled with -fmad=false: the arithmetic is the stage
+// functions' (mp_stages*.h), operation for operation.
+#pragma once
+
+#include <cuda_runtime.h>
+
+#include "mp_stages.h"
+
+namespace mpenv {
+
+struct KernelArgs {
+    Ctx ctx;                 // ctx.bvh points at the GLOBAL copies
+    uint32_t bvhNodeWords;   // 32-bit words of node data
+    uint32_t bvhVertWords;   // 32-bit words of vertex data (incl. the pad triangle)
+    int32_t bvhInSmem;       // 1: stage into shared memory, 0: traverse from global / L2
+};
+
+// Copies the BVH into dynamic shared memory and returns a view onto it.
+__device__ __forceinline__ BVHView stageBVH(const KernelArgs &ka, uint32_t *smem)
+{
+    BVHView v = ka.ctx.bvh;
+    if (!ka.bvhInSmem) return v;
+    const uint32_t *gn = reinterpret_cast<const uint32_t *>(ka.ctx.bvh.nodes);
+    const uint32_t *gv = reinterpret_cast<const uint32_t *>(ka.ctx.bvh.verts);
+    uint32_t *sn = smem;
+    uint32_t *sv = smem + ka.bvhNodeWords;
+    // 128-bit copies: node data is a multiple of 64 bytes; the vertex tail is
+    // finished word by word.
+    const uint32_t n4 = ka.bvhNodeWords / 4;
+    for (uint32_t i = threadIdx.x; i < n4; i += blockDim.x)
+        reinterpret_cast<uint4 *>(sn)[i] = __ldg(reinterpret_cast<const uint4 *>(gn) + i);
+    const uint32_t v4 = ka.bvhVertWords / 4;
+    for (uint32_t i = threadIdx.x; i < v4; i += blockDim.x)
+        reinterpret_cast<uint4 *>(sv)[i] = __ldg(reinterpret_cast<const uint4 *>(gv) + i);
+    for (uint32_t i = v4 * 4 + threadIdx.x; i < ka.bvhVertWords; i += blockDim.x) sv[i] = __ldg(gv + i);
+    __syncthreads();
+    v.nodes = reinterpret_cast<const BVHNode *>(sn);
+    v.verts = reinterpret_cast<const Vec3 *>(sv);
+    return v;
+}
+
+__global__ void __launch_bounds__(128) k_ctor(KernelArgs ka)
+{
+    const int W = (int)ka.ctx.cfg.numWorlds;
+    for (int w = blockIdx.x * blockDim.x + threadIdx.x; w < W; w += gridDim.x * blockDim.x)
+        ctorWorld(ka.ctx, w);
+}
+
+__global__ void __launch_bounds__(128) k_force_reset(KernelArgs ka)
+{
+    const int W = (int)ka.ctx.cfg.numWorlds;
+    for (int w = blockIdx.x * blockDim.x + threadIdx.x; w < W; w += gridDim.x * blockDim.x)
+        ka.ctx.p.resetFlag[w] = 1;
+}
+
+__global__ void __launch_bounds__(128) k_reset(KernelArgs ka)
+{
+    const int W = (int)ka.ctx.cfg.numWorlds;
+    for (int w = blockIdx.x * blockDim.x + threadIdx.x; w < W; w += gridDim.x * blockDim.x)
+        resetSystem(ka.ctx, w);
+}
+
+__global__ void __launch_bounds__(128) k_move(KernelArgs ka)
+{
+    extern __shared__ uint4 smem_raw[];
+    Ctx c = ka.ctx;
+    c.bvh = stageBVH(ka, reinterpret_cast<uint32_t *>(smem_raw));
+    const int N = (int)c.cfg.numWorlds * kAgents;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < N; i += gridDim.x * blockDim.x)
+        stageMove(c, i);
+}
+
+__global__ void __launch_bounds__(128) k_fire(KernelArgs ka)
+{
+    extern __shared__ uint4 smem_raw[];
+    Ctx c = ka.ctx;
+    c.bvh = stageBVH(ka, reinterpret_cast<uint32_t *>(smem_raw));
+    const int N = (int)c.cfg.numWorlds * kAgents;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < N; i += gridDim.x * blockDim.x) {
+        const int w = i / kAgents, a = i - w * kAgents;
+        stageFire(c, w, a, c.p.pos + (size_t)w * kAgents);
+    }
+}
+
+__global__ void __launch_bounds__(64) k_world(KernelArgs ka)
+{
+    const int W = (int)ka.ctx.cfg.numWorlds;
+    for (int w = blockIdx.x * blockDim.x + threadIdx.x; w < W; w += gridDim.x * blockDim.x)
+        stageWorld(ka.ctx, w);
+}
+
+__global__ void __launch_bounds__(128) k_los(KernelArgs ka)
+{
+    extern __shared__ uint4 smem_raw[];
+    Ctx c = ka.ctx;
+    c.bvh = stageBVH(ka, reinterpret_cast<uint32_t *>(smem_raw));
+    const int P = (int)c.cfg.numWorlds * kAgents * kTeamSize;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < P; i += gridDim.x * blockDim.x) {
+        const int idx = i / kTeamSize, j = i - idx * kTeamSize;
+        const int w = idx / kAgents, a = idx - w * kAgents;
+        c.p.canSee[(size_t)idx * 8 + j] = visibilityPair(c, w, a, j, c.p.pos + (size_t)w * kAgents) ? 1 : 0;
+    }
+}
+
+__global__ void __launch_bounds__(128) k_obs(KernelArgs ka)
+{
+    const Ctx &c = ka.ctx;
+    const int N = (int)c.cfg.numWorlds * kAgents;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < N; i += gridDim.x * blockDim.x) {
+        const int w = i / kAgents, a = i - w * kAgents;
+        stageObs(c, w, a);
+    }
+}
+
+__global__ void __launch_bounds__(128) k_fullteam(KernelArgs ka)
+{
+    const Ctx &c = ka.ctx;
+    const int T = (int)c.cfg.numWorlds * 2;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < T; i += gridDim.x * blockDim.x)
+        stageFullTeamObs(c, i / 2, i & 1);
+}
+
+__global__ void __launch_bounds__(160) k_lidar(KernelArgs ka)
+{
+    extern __shared__ uint4 smem_raw[];
+    Ctx c = ka.ctx;
+    c.bvh = stageBVH(ka, reinterpret_cast<uint32_t *>(smem_raw));
+    const long long R = (long long)c.cfg.numWorlds * kAgents * 80;
+    for (long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x; g < R;
+         g += (long long)gridDim.x * blockDim.x) {
+        const int idx = (int)(g / 80), ray = (int)(g - (long long)idx * 80);
+        const int w = idx / kAgents, a = idx - w * kAgents;
+        LidarSample s = lidarRay(c, w, a, ray, c.p.pos + (size_t)w * kAgents);
+        float4 v = make_float4(s.depth, s.isWall, s.isTeammate, s.isOpponent);
+        if (ray < 64) reinterpret_cast<float4 *>(c.p.fwdLidar)[(size_t)idx * 64 + ray] = v;
+        else reinterpret_cast<float4 *>(c.p.rearLidar)[(size_t)idx * 16 + (ray - 64)] = v;
+    }
+}
+
+// Episode statistics for the multi-GPU allreduce: per-device sums
+// over worlds.  out[0] worlds, [1] episodes finished this step, [2..4] wins
+// team0 / team1 / draw among them, [5..6] kills, [7..8] objective points of the
+// finished episodes, [9] agents alive, [10] sum(done), [11] sum(reward) in 1e-6
+// units, [12] sum(cur_step); the rest reserved.
+__global__ void __launch_bounds__(256) k_stats(KernelArgs ka, unsigned long long *out)
+{
+    const Ctx &c = ka.ctx;
+    const int W = (int)c.cfg.numWorlds;
+    long long acc[13];
+    for (int k = 0; k < 13; k++) acc[k] = 0;
+    for (int w = blockIdx.x * blockDim.x + threadIdx.x; w < W; w += gridDim.x * blockDim.x) {
+        acc[0] += 1;
+        const MatchResult &mr = c.p.matchResult[w];
+        // done is exported per agent; row 0 of the world carries the episode flag
+        if (c.p.done[w * kAgents]) {
+            acc[1] += 1;
+            if (mr.winResult >= 0 && mr.winResult <= 2) acc[2 + mr.winResult] += 1;
+            acc[5] += mr.teamTotalKills[0]; acc[6] += mr.teamTotalKills[1];
+            acc[7] += mr.teamObjectivePoints[0]; acc[8] += mr.teamObjectivePoints[1];
+        }
+        for (int a = 0; a < kAgents; a++) {
+            const int idx = w * kAgents + a;
+            acc[9] += c.p.alive[idx] != 0.f ? 1 : 0;
+            acc[10] += c.p.done[idx];
+            acc[11] += (long long)llrintf(c.p.reward[idx] * 1.0e6f);
+        }
+        acc[12] += c.p.world[w].match.curStep;
+    }
+    for (int k = 0; k < 13; k++) {
+        long long v = acc[k];
+        for (int off = 16; off > 0; off >>= 1) v += __shfl_down_sync(0xFFFFFFFFu, v, off);
+        if ((threadIdx.x & 31) == 0 && v != 0) atomicAdd(out + k, (unsigned long long)v);
+    }
+}
+
+}  // namespace mpenv

@@ -495,3 +495,125 @@ def random_actions(step, num_worlds, world_id_offset=0, seed=1234, stress=False,
     discrete = np.stack([move_amount, move_angle, fire, stand], axis=1)
     discrete_aim = np.stack([yaw, pitch], axis=1)
     return discrete, discrete_aim
+
+
+def seek_policy(sim, step, num_worlds, world_id_offset=0, seed=77):
+    """A scripted policy that produces combat (the uniform random stream almost
+    never brings the teams into contact): turn towards a visible opponent and
+    fire, otherwise run towards the zone centre; a third of the decisions stay
+    random.  Computed from `sim`'s exported observations, so feed the SAME
+    arrays to every implementation under comparison."""
+    n = num_worlds * AGENTS
+    self_obs = sim.export("self_obs")
+    opp = sim.export("opponent_obs").reshape(n, 6, 32)
+    mag = sim.export("magazine")
+    rnd_d, rnd_a = random_actions(step, num_worlds, world_id_offset, seed)
+    yaw_amt = np.pi * np.array([0, 1 / 256, 1 / 128, 1 / 64, 1 / 32, 1 / 16, 1 / 8])
+    pitch_amt = np.pi * np.array([0, 1 / 128, 1 / 64, 1 / 32])
+
+    def bucket(delta, amounts, centre):
+        k = np.searchsorted(amounts, np.abs(delta), side="right") - 1
+        return (centre + np.sign(delta).astype(np.int64) * k).astype(np.int32)
+
+    los = opp[:, :, 30] > 0
+    dist = np.where(los, opp[:, :, 23], np.inf)
+    tgt = np.argmin(dist, axis=1)
+    has_tgt = los.any(axis=1)
+    rows = np.arange(n)
+    yaw_d = np.where(has_tgt, opp[rows, tgt, 24], self_obs[:, 31])
+    pitch_d = np.where(has_tgt, opp[rows, tgt, 25], 0.0)
+    discrete = np.zeros((n, 4), np.int32)
+    discrete[:, 0] = np.where(has_tgt, 0, 2)                 # stop to shoot, else run
+    discrete[:, 1] = 0                                       # forward
+    discrete[:, 2] = np.where(mag[:, 0] == 0, 2, np.where(has_tgt, 1, 0))
+    discrete[:, 3] = 0
+    aim = np.stack([bucket(yaw_d, yaw_amt, 6), bucket(pitch_d, pitch_amt, 3)], axis=1)
+    use_rnd = (rnd_d[:, 1] % 3 == 0) & ~has_tgt
+    discrete = np.where(use_rnd[:, None], rnd_d, discrete)
+    aim = np.where(use_rnd[:, None], rnd_a, aim)
+    return discrete.astype(np.int32), aim.astype(np.int32)
+
+
+# ------------------------------------------------------------------ product
+class MpenvConfig(C.Structure):
+    _fields_ = [("gpu_id", C.c_int32), ("num_worlds", C.c_uint32), ("rand_seed", C.c_uint32),
+                ("auto_reset", C.c_int32), ("sim_flags", C.c_uint32), ("task_type", C.c_uint32),
+                ("team_size", C.c_uint32), ("num_pbt_policies", C.c_uint32),
+                ("policy_history_size", C.c_uint32), ("scene_dir", C.c_char_p),
+                ("world_id_offset", C.c_uint32), ("enable_full_team", C.c_uint32)]
+
+
+class TensorDesc(C.Structure):
+    _fields_ = [("dev_ptr", C.c_void_p), ("dtype", C.c_int32), ("ndim", C.c_int32),
+                ("dims", C.c_int64 * 4), ("gpu_id", C.c_int32)]
+
+
+def load_product():
+    """Loads libmpenv_b200.so (built by __graft_entry__.build()); no fallback."""
+    if not os.path.exists(PRODUCT_SO):
+        raise RuntimeError(f"{PRODUCT_SO} is missing: run `python -c 'import __graft_entry__ as g; g.build()'`")
+    L = C.CDLL(PRODUCT_SO)
+    L.mpenv_create.argtypes = [C.POINTER(MpenvConfig), C.POINTER(C.c_void_p)]
+    for f in ("mpenv_destroy", "mpenv_init", "mpenv_step", "mpenv_sync"):
+        getattr(L, f).argtypes = [C.c_void_p]
+    L.mpenv_step_async.argtypes = [C.c_void_p, C.c_void_p]
+    L.mpenv_init_async.argtypes = [C.c_void_p, C.c_void_p]
+    L.mpenv_tensor.argtypes = [C.c_void_p, C.c_uint32, C.POINTER(TensorDesc)]
+    L.mpenv_write_tensor_async.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint64]
+    L.mpenv_read_tensor_async.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint64]
+    L.mpenv_get_world_state.argtypes = [C.c_void_p, C.c_uint32, C.POINTER(WorldState)]
+    L.mpenv_last_error.restype = C.c_char_p
+    L.mpenv_last_error.argtypes = [C.c_void_p]
+    L.mpenv_launches_per_step.argtypes = [C.c_void_p, C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]
+    L.mpenv_episode_stats_async.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(C.c_void_p)]
+    L.mpenv_host_alloc.argtypes = [C.c_uint64, C.POINTER(C.c_void_p)]
+    L.mpenv_host_free.argtypes = [C.c_void_p]
+    L.mpenv_trigger_reset.argtypes = [C.c_void_p, C.c_int32]
+    return L
+
+
+class GpuSim(_SimBase):
+    """The product: libmpenv_b200.so through its C ABI, host buffers in and out."""
+
+    def __init__(self, num_worlds, rand_seed=10, auto_reset=False, sim_flags=0, world_id_offset=0,
+                 full_team=True, scene=SCENE, gpu_id=0):
+        self.lib = load_product()
+        self._scene = scene.encode()
+        cfg = MpenvConfig(gpu_id, num_worlds, rand_seed, int(auto_reset), sim_flags, 2, 6, 0, 1,
+                          self._scene, world_id_offset, int(full_team))
+        self.h = C.c_void_p()
+        rc = self.lib.mpenv_create(C.byref(cfg), C.byref(self.h))
+        if rc != 0:
+            raise RuntimeError(f"mpenv_create failed ({rc}): {self.lib.mpenv_last_error(None).decode()}")
+        self.num_worlds = num_worlds
+
+    def _check(self, rc, what):
+        if rc != 0:
+            raise RuntimeError(f"{what} failed ({rc}): {self.lib.mpenv_last_error(self.h).decode()}")
+
+    def close(self):
+        if self.h:
+            self.lib.mpenv_destroy(self.h)
+            self.h = None
+
+    def init(self):
+        self._check(self.lib.mpenv_init(self.h), "mpenv_init")
+
+    def step(self):
+        self._check(self.lib.mpenv_step(self.h), "mpenv_step")
+
+    def _read(self, eid, arr):
+        self._check(self.lib.mpenv_read_tensor_async(self.h, eid, arr.ctypes.data, arr.nbytes), "read")
+        self._check(self.lib.mpenv_sync(self.h), "sync")
+
+    def _write(self, eid, arr):
+        self._check(self.lib.mpenv_write_tensor_async(self.h, eid, arr.ctypes.data, arr.nbytes), "write")
+        self._check(self.lib.mpenv_sync(self.h), "sync")
+
+    def _state(self, w, ws):
+        self._check(self.lib.mpenv_get_world_state(self.h, w, C.byref(ws)), "get_world_state")
+
+    def launches(self):
+        a, b = C.c_uint32(), C.c_uint32()
+        self.lib.mpenv_launches_per_step(self.h, C.byref(a), C.byref(b))
+        return a.value, b.value
