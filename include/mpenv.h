@@ -171,6 +171,13 @@ int mpenv_get_world_state(mpenv_handle *h, uint32_t world_idx, mpenv_world_state
 /* Number of kernel launches issued by one step / one init (for bench accounting). */
 int mpenv_launches_per_step(mpenv_handle *h, uint32_t *step_launches, uint32_t *init_launches);
 
+/* Measurement aid: runs ONE step as individual launches on the handle's stream
+ * with a CUDA event pair around each kernel; writes up to `cap` durations (ms)
+ * and the matching kernel names.  Synchronous.  Same kernels and results as
+ * mpenv_step. */
+int mpenv_step_timed(mpenv_handle *h, float *kernel_ms, const char **kernel_names, uint32_t cap,
+                     uint32_t *count);
+
 const char *mpenv_last_error(mpenv_handle *h);   /* h may be NULL: last create() error */
 
 /* ---- map section: host-side asset loading (Impl::init's loadMapData /

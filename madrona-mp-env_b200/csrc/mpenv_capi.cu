@@ -515,6 +515,37 @@ int mpenv_get_world_state(mpenv_handle *h, uint32_t world_idx, mpenv_world_state
     return MPENV_OK;
 }
 
+int mpenv_step_timed(mpenv_handle *h, float *kernel_ms, const char **kernel_names, uint32_t cap, uint32_t *count)
+{
+    if (!h || !kernel_ms || !count) return MPENV_ERR_INVALID;
+    MP_CUDA(h, cudaSetDevice(h->device));
+    cudaStream_t s = h->stream;
+    struct Item { const char *name; };
+    const char *names[8];
+    cudaEvent_t ev[9];
+    for (int i = 0; i < 9; i++) MP_CUDA(h, cudaEventCreate(&ev[i]));
+    uint32_t n = 0;
+    MP_CUDA(h, cudaEventRecord(ev[0], s));
+    k_move<<<h->gridMove, 128, h->bvhSmemBytes, s>>>(h->ka); names[n++] = "k_move"; cudaEventRecord(ev[n], s);
+    k_fire<<<h->gridFire, 128, h->bvhSmemBytes, s>>>(h->ka); names[n++] = "k_fire"; cudaEventRecord(ev[n], s);
+    k_world<<<h->gridWorld, 64, 0, s>>>(h->ka); names[n++] = "k_world"; cudaEventRecord(ev[n], s);
+    k_los<<<h->gridLos, 128, h->bvhSmemBytes, s>>>(h->ka); names[n++] = "k_los"; cudaEventRecord(ev[n], s);
+    k_obs<<<h->gridObs, 128, 0, s>>>(h->ka); names[n++] = "k_obs"; cudaEventRecord(ev[n], s);
+    if (h->fullTeam) {
+        k_fullteam<<<h->gridTeam, 128, 0, s>>>(h->ka); names[n++] = "k_fullteam"; cudaEventRecord(ev[n], s);
+    }
+    k_lidar<<<h->gridLidar, 160, h->bvhSmemBytes, s>>>(h->ka); names[n++] = "k_lidar"; cudaEventRecord(ev[n], s);
+    MP_CUDA(h, cudaGetLastError());
+    MP_CUDA(h, cudaStreamSynchronize(s));
+    for (uint32_t i = 0; i < n && i < cap; i++) {
+        MP_CUDA(h, cudaEventElapsedTime(&kernel_ms[i], ev[i], ev[i + 1]));
+        if (kernel_names) kernel_names[i] = names[i];
+    }
+    for (int i = 0; i < 9; i++) cudaEventDestroy(ev[i]);
+    *count = n < cap ? n : cap;
+    return MPENV_OK;
+}
+
 int mpenv_launches_per_step(mpenv_handle *h, uint32_t *step_launches, uint32_t *init_launches)
 {
     if (!h) return MPENV_ERR_INVALID;
