@@ -165,6 +165,9 @@ int mpenv_set_uniform_agent_policy(mpenv_handle *h, int32_t policy_idx);
  * owned by the handle and returns its pointer; stream-ordered. */
 #define MPENV_NUM_STATS 16
 int mpenv_episode_stats_async(mpenv_handle *h, void *cuda_stream, int64_t **dev_out);
+/* Synchronous host variant: reduces on the handle's stream and copies the
+ * MPENV_NUM_STATS values to `host_out`. */
+int mpenv_episode_stats(mpenv_handle *h, int64_t *host_out);
 
 /* Test / debug surface: full per-world state (see mpenv_state.h). */
 int mpenv_get_world_state(mpenv_handle *h, uint32_t world_idx, mpenv_world_state *out);

@@ -491,6 +491,17 @@ int mpenv_episode_stats_async(mpenv_handle *h, void *cuda_stream, int64_t **dev_
     return MPENV_OK;
 }
 
+int mpenv_episode_stats(mpenv_handle *h, int64_t *host_out)
+{
+    if (!h || !host_out) return MPENV_ERR_INVALID;
+    int64_t *dev = nullptr;
+    int rc = mpenv_episode_stats_async(h, h->stream, &dev);
+    if (rc != MPENV_OK) return rc;
+    MP_CUDA(h, cudaMemcpyAsync(host_out, dev, sizeof(int64_t) * MPENV_NUM_STATS, cudaMemcpyDeviceToHost, h->stream));
+    MP_CUDA(h, cudaStreamSynchronize(h->stream));
+    return MPENV_OK;
+}
+
 int mpenv_get_world_state(mpenv_handle *h, uint32_t world_idx, mpenv_world_state *out)
 {
     if (!h || !out || world_idx >= h->cfg.num_worlds) return MPENV_ERR_INVALID;

@@ -617,3 +617,33 @@ class GpuSim(_SimBase):
         a, b = C.c_uint32(), C.c_uint32()
         self.lib.mpenv_launches_per_step(self.h, C.byref(a), C.byref(b))
         return a.value, b.value
+
+    def episode_stats(self):
+        """int64[16] episode statistics of this shard (k_stats), synchronous."""
+        host = np.empty(16, np.int64)
+        self.lib.mpenv_episode_stats.argtypes = [C.c_void_p, C.c_void_p]
+        self._check(self.lib.mpenv_episode_stats(self.h, host.ctypes.data), "episode_stats")
+        return host
+
+
+def episode_stats_host(sim):
+    """numpy mirror of k_stats (step_kernels.cuh): the per-shard input of the
+    multi-GPU allreduce, computed from any _SimBase's exports + world state."""
+    W = sim.num_worlds
+    done = sim.export("done").reshape(W, AGENTS)
+    mr = sim.export("match_result")
+    alive = sim.export("alive").reshape(W, AGENTS)
+    reward = sim.export("reward").reshape(W, AGENTS)
+    out = np.zeros(16, np.int64)
+    out[0] = W
+    fin = done[:, 0] != 0
+    out[1] = fin.sum()
+    for k in range(3):
+        out[2 + k] = (fin & (mr[:, 0] == k)).sum()
+    out[5:7] = mr[fin, 1:3].sum(axis=0)
+    out[7:9] = mr[fin, 3:5].sum(axis=0)
+    out[9] = (alive != 0).sum()
+    out[10] = done.sum()
+    out[11] = np.rint(reward.astype(np.float32) * np.float32(1.0e6)).astype(np.int64).sum()
+    out[12] = sum(sim.world_state(w)["cur_step"] for w in range(W))
+    return out

@@ -110,3 +110,124 @@ def test_large_batch_properties():
         orc.close()
     finally:
         gpu.close()
+
+
+def test_golden_fixture_gpu():
+    """The CUDA path against the committed oracle fixture (tests/golden/, made by
+    make_golden.py in the container that has the reference)."""
+    import json, os
+    gdir = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+    spec = json.load(open(os.path.join(gdir, "rollouts.json")))["combat_w8"]
+    gold = np.load(os.path.join(gdir, "state_combat_w8_first2.npz"))
+    W = spec["worlds"]
+    gpu = S.GpuSim(W, rand_seed=spec["seed"], auto_reset=spec["auto_reset"])
+    try:
+        gpu.init()
+        for s in range(spec["steps"]):
+            d, a = S.seek_policy(gpu, s, W)
+            gpu.set_actions(d, a); gpu.step()
+        for name in S.STEP_OUTPUTS:
+            x = gpu.export(name)[: len(gold[name])]
+            assert np.array_equal(x.view(np.int32), gold[name].view(np.int32)), name
+        assert gpu.export("match_result")[:, 1:5].sum() == spec["match_result_sum"]
+    finally:
+        gpu.close()
+
+
+def test_raycast_stress_bit_exact():
+    """BASELINE.json configs[3] at oracle-checkable size: every agent fires every step
+    (reload when the magazine reads 0), LOS + lidar on."""
+    W = 16
+    gpu = S.GpuSim(W, auto_reset=True)
+    orc = S.Oracle(W, auto_reset=True, det=True, num_threads=0)
+    try:
+        gpu.init(); orc.init()
+        for s in range(150):
+            d, a = S.random_actions(s, W, stress=True, magazine=orc.export("magazine"))
+            for sim in (gpu, orc):
+                sim.set_actions(d, a); sim.step()
+            if s % 10 == 9:
+                assert_same(gpu, orc, W, f"stress step {s}")
+    finally:
+        gpu.close(); orc.close()
+
+
+def test_episode_stats_kernel():
+    """k_stats (input of the multi-GPU allreduce) against its numpy mirror."""
+    W = 16
+    gpu = S.GpuSim(W, auto_reset=True)
+    try:
+        gpu.init()
+        for s in range(40):
+            d, a = S.seek_policy(gpu, s, W)
+            if s == 20:
+                gpu.set_export("reset", (np.arange(W) % 3 == 0).astype(np.int32).reshape(W, 1))
+            gpu.set_actions(d, a); gpu.step()
+            assert np.array_equal(gpu.episode_stats(), S.episode_stats_host(gpu)), f"step {s}"
+    finally:
+        gpu.close()
+
+
+def test_python_manager_zero_copy_and_stream_step():
+    """BASELINE.json configs[4] coupling: the Python SimManager mirror (bindings.cpp) --
+    action tensors aliased zero-copy by torch (DLPack / __cuda_array_interface__),
+    stream-ordered step, and gpuStreamStep-style buffer copies (mgr.cpp:614-645)."""
+    import ctypes as C
+    import torch
+    import madrona_mp_env as mp
+    W = 8
+    n = W * 12
+    mgr = mp.SimManager(mp.ExecMode.CUDA, 0, W, 10, False, 0, mp.Task.Zone, 6, 0, 1, S.SCENE)
+    orc = S.Oracle(W, det=True, num_threads=0)
+    try:
+        act = mgr.pvp_discrete_action_tensor().to_torch()
+        aim = torch.from_dlpack(mgr.pvp_discrete_aim_action_tensor())
+        assert act.shape == (n, 4) and act.dtype == torch.int32 and aim.shape == (n, 2)
+        assert act.data_ptr() == mgr.pvp_discrete_action_tensor().ptr, "zero copy"
+        ti = mgr.train_interface()
+        assert list(ti["inputs"]) == ["discrete", "aim", "resets", "sim_ctrl", "policy_assignments"]
+        assert ti["outputs"]["self"].shape == (n, 43) and ti["outputs"]["fwd_lidar"].shape == (n, 2, 32, 4)
+        assert ti["outputs"]["episode_results"].shape == (W, 30)
+        mgr.init(); orc.init()
+        stream = torch.cuda.Stream()
+        self_obs = mgr.self_observation_tensor().to_torch()
+        for s in range(25):
+            d, a = S.random_actions(s, W)
+            with torch.cuda.stream(stream):
+                act.copy_(torch.from_numpy(d).cuda(), non_blocking=True)
+                aim.copy_(torch.from_numpy(a).cuda(), non_blocking=True)
+                mgr.step_async(stream.cuda_stream)
+            stream.synchronize()
+            orc.set_actions(d, a); orc.step()
+        assert np.array_equal(self_obs.cpu().numpy().view(np.int32), orc.export("self_obs").view(np.int32))
+        # gpuStreamStep: caller-owned device buffers in train-interface order
+        lib, h = mgr._lib, mgr._h
+        arr = C.POINTER(mp._NamedTensor)()
+        cnt = C.c_uint32()
+        lib.mpenv_train_interface(h, C.byref(arr), C.byref(cnt))
+        bufs, keep = (C.c_void_p * cnt.value)(), {}
+        for i in range(cnt.value):
+            name = arr[i].name.decode()
+            t = (ti["inputs"] if arr[i].is_input else ti["outputs"])[name]
+            if name in ("agent_map", "unmasked_agent_map"):
+                bufs[i] = None
+                continue
+            buf = torch.zeros(t.shape, dtype=torch.int32 if t.typestr == "<i4" else torch.float32, device="cuda")
+            if arr[i].is_input:
+                buf.copy_(t.to_torch())
+            keep[name] = buf
+            bufs[i] = buf.data_ptr()
+        d, a = S.random_actions(25, W)
+        keep["discrete"].copy_(torch.from_numpy(d).cuda()); keep["aim"].copy_(torch.from_numpy(a).cuda())
+        torch.cuda.synchronize()
+        lib.mpenv_stream_step.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+        assert lib.mpenv_stream_step(h, C.c_void_p(stream.cuda_stream), bufs) == 0
+        stream.synchronize()
+        orc.set_actions(d, a); orc.step()
+        for ours, theirs in (("self", "self_obs"), ("rewards", "reward"), ("fwd_lidar", "fwd_lidar"),
+                             ("opponents_last_known", "opponent_last_known_obs"), ("episode_results", "match_result")):
+            x = keep[ours].cpu().numpy().reshape(orc.export(theirs).shape)
+            assert np.array_equal(x.view(np.int32), orc.export(theirs).view(np.int32)), ours
+    finally:
+        orc.close()
+        del mgr
