@@ -7,7 +7,10 @@
 #include <string>
 #include <vector>
 
+#include <cstdlib>
+
 #include "step_kernels.cuh"
+#include "ray_kernels.cuh"
 #include "assets.h"
 #include "sim_layout.h"
 #include "../../include/mpenv.h"
@@ -40,6 +43,10 @@ struct mpenv_handle {
     cudaGraphExec_t stepGraph = nullptr;
     cudaGraphExec_t initGraph = nullptr;
     bool fullTeam = false;
+    bool poolLidar = false;                  // warp-pooled ray engine (ray_kernels.cuh)
+    size_t lidarPoolSmem = 0;
+    int gridLidarPool = 0;
+    void (*lidarPoolKernel)(KernelArgs) = nullptr;
     // launch geometry
     int gridMove = 0, gridFire = 0, gridWorld = 0, gridLos = 0, gridObs = 0, gridTeam = 0, gridLidar = 0,
         gridSmall = 0;
@@ -79,6 +86,12 @@ int gridFor(mpenv_handle *h, K kernel, int block, size_t smem, long long items)
     return (int)(want < cap ? want : cap);
 }
 
+void launchLidar(mpenv_handle *h, cudaStream_t s)
+{
+    if (h->poolLidar) h->lidarPoolKernel<<<h->gridLidarPool, kLidarWarpsPerCTA * 32, h->lidarPoolSmem, s>>>(h->ka);
+    else k_lidar<<<h->gridLidar, 160, h->bvhSmemBytes, s>>>(h->ka);
+}
+
 // The obs phase shared by the Init and Step graphs (resetAndObsTasks,
 // sim.cpp:5174-5320): visibility -> masks + observations -> full-team -> lidar.
 uint32_t launchObsPhase(mpenv_handle *h, cudaStream_t s)
@@ -87,7 +100,7 @@ uint32_t launchObsPhase(mpenv_handle *h, cudaStream_t s)
     k_los<<<h->gridLos, 128, h->bvhSmemBytes, s>>>(h->ka); n++;
     k_obs<<<h->gridObs, 128, 0, s>>>(h->ka); n++;
     if (h->fullTeam) { k_fullteam<<<h->gridTeam, 128, 0, s>>>(h->ka); n++; }
-    k_lidar<<<h->gridLidar, 160, h->bvhSmemBytes, s>>>(h->ka); n++;
+    launchLidar(h, s); n++;
     return n;
 }
 
@@ -299,6 +312,22 @@ int mpenv_create(const mpenv_config *cfg, mpenv_handle **out)
     h->gridTeam = gridFor(h, k_fullteam, 128, 0, W * 2);
     h->gridLidar = gridFor(h, k_lidar, 160, h->bvhSmemBytes, N * 80);
     h->gridSmall = gridFor(h, k_reset, 128, 0, W);
+
+    // warp-pooled ray kernels: need the re-encoded BVH + per-warp pools in shared memory
+    const char *kmode = getenv("MPENV_KERNELS");
+    const bool legacy = kmode && strcmp(kmode, "legacy") == 0;
+    h->lidarPoolSmem = lidarPoolSmemBytes(ka.ctx.bvh.numNodes, ka.ctx.bvh.numTris);
+    h->poolLidar = !legacy && h->lidarPoolSmem <= 200 * 1024;
+    if (h->poolLidar) {
+        // leaf-batch threshold of the traversal loop (ray_fast.cuh); tunable for experiments
+        const char *lb = getenv("MPENV_LEAF_BATCH");
+        const int batch = lb ? atoi(lb) : kLeafBatch;
+        h->lidarPoolKernel = batch <= 1 ? k_lidar_pool<1> : batch <= 6 ? k_lidar_pool<6> :
+                             batch <= 10 ? k_lidar_pool<10> : batch <= 16 ? k_lidar_pool<16> : k_lidar_pool<24>;
+        MP_CREATE(cudaFuncSetAttribute(h->lidarPoolKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->lidarPoolSmem));
+        h->gridLidarPool = gridFor(h, h->lidarPoolKernel, kLidarWarpsPerCTA * 32, h->lidarPoolSmem,
+                                   (N / 2) * 32);
+    }
 
     // Sim::Sim for every world (sim.cpp:5850-5980)
     k_ctor<<<h->gridSmall, 128, 0, h->stream>>>(ka);
@@ -545,7 +574,7 @@ int mpenv_step_timed(mpenv_handle *h, float *kernel_ms, const char **kernel_name
     if (h->fullTeam) {
         k_fullteam<<<h->gridTeam, 128, 0, s>>>(h->ka); names[n++] = "k_fullteam"; cudaEventRecord(ev[n], s);
     }
-    k_lidar<<<h->gridLidar, 160, h->bvhSmemBytes, s>>>(h->ka); names[n++] = "k_lidar"; cudaEventRecord(ev[n], s);
+    launchLidar(h, s); names[n++] = "k_lidar"; cudaEventRecord(ev[n], s);
     MP_CUDA(h, cudaGetLastError());
     MP_CUDA(h, cudaStreamSynchronize(s));
     for (uint32_t i = 0; i < n && i < cap; i++) {

@@ -1,0 +1,400 @@
+// ray_fast.cuh -- warp-pooled closest-hit ray engine for the ray-heavy kernels
+// (k_lidar, k_los).  Device only.
+//
+// Same results as mp_geom.h's bvhTraceRay / traceRayWorld (reference
+// mesh_bvh.inl:110-208, 360-554; utils.cpp:10-72), bit for bit: every float
+// expression is the reference's, and each ray visits nodes, children and
+// triangles in the reference's ORDER (LIFO stack, children 0..3, leaves tested
+// inline) -- the order decides which of two coplanar triangles' 1-ulp-apart t
+// values wins.  What changes is the execution shape:
+//
+//  * the BVH is re-encoded once per CTA into shared memory as FastNode /
+//    FastTri: quantised bounds pre-converted to float (exact), the 2^exp scales
+//    materialised, one 32-byte record per child, triangles padded to 48 bytes:
+//    traversal is LDS.128 only -- no generic loads, no I2F, no byte extracts;
+//  * a node visit computes all four child slab tests in one branch-free block.
+//    The reference's test  t_near <= min(t_far_xyz, t_max)  is split into
+//    (t_near <= t_far_xyz), evaluated at the visit, and (t_near <= t_max),
+//    re-evaluated when the child's turn comes (t_max may have shrunk since);
+//    for non-NaN operands the two forms are identical;
+//  * rays are pulled from a per-warp pool in shared memory: a lane that
+//    finishes its ray fetches the next one, so a warp's 32 lanes stay busy
+//    until the pool drains instead of idling behind the longest ray;
+//  * per-ray constants (reciprocals, Woop shear, axis permutation) are computed
+//    once per unique direction by converged lanes and parked in the pool.
+#pragma once
+
+#include <cuda_runtime.h>
+
+#include "mp_geom.h"
+
+namespace mpenv {
+
+struct FastChild {
+    float qMinX, qMinY, qMinZ, qMaxX, qMaxY, qMaxZ;
+    int32_t child;          // kBVHSentinel, leaf (bit 31) or node index
+    int32_t triSize;
+};
+struct __align__(16) FastNode {
+    float minX, minY, minZ, sX;
+    float sY, sZ;
+    int32_t pad0, pad1;
+    FastChild c[4];
+};
+static_assert(sizeof(FastNode) == 160, "FastNode is 10 x 16 bytes");
+struct __align__(16) FastTri { float v[12]; };   // a.xyz b.xyz c.xyz + pad
+
+struct FastBVH {
+    const FastNode *nodes;
+    const FastTri *tris;
+};
+
+__host__ __device__ inline size_t fastBVHBytes(uint32_t num_nodes, uint32_t num_tris)
+{
+    return (size_t)num_nodes * sizeof(FastNode) + (size_t)(num_tris + 1) * sizeof(FastTri);
+}
+
+// Re-encodes the reference-format BVH (global memory) into `smem`.
+__device__ __forceinline__ FastBVH stageFastBVH(const BVHView &g, void *smem)
+{
+    FastNode *sn = reinterpret_cast<FastNode *>(smem);
+    FastTri *st = reinterpret_cast<FastTri *>(sn + g.numNodes);
+    for (uint32_t i = threadIdx.x; i < g.numNodes * 4u; i += blockDim.x) {
+        const uint32_t n = i >> 2, k = i & 3u;
+        const BVHNode &src = g.nodes[n];
+        FastChild c;
+        c.qMinX = (float)src.qMinX[k]; c.qMinY = (float)src.qMinY[k]; c.qMinZ = (float)src.qMinZ[k];
+        c.qMaxX = (float)src.qMaxX[k]; c.qMaxY = (float)src.qMaxY[k]; c.qMaxZ = (float)src.qMaxZ[k];
+        c.child = src.children[k];
+        c.triSize = src.triSize[k];
+        sn[n].c[k] = c;
+        if (k == 0) {
+            sn[n].minX = src.minX; sn[n].minY = src.minY; sn[n].minZ = src.minZ;
+            sn[n].sX = u2f((uint32_t)((int32_t)src.expX + 127) << 23);
+            sn[n].sY = u2f((uint32_t)((int32_t)src.expY + 127) << 23);
+            sn[n].sZ = u2f((uint32_t)((int32_t)src.expZ + 127) << 23);
+            sn[n].pad0 = 0; sn[n].pad1 = 0;
+        }
+    }
+    const float *gv = reinterpret_cast<const float *>(g.verts);
+    for (uint32_t i = threadIdx.x; i < (g.numTris + 1u) * 12u; i += blockDim.x) {
+        const uint32_t t = i / 12u, k = i - t * 12u;
+        st[t].v[k] = k < 9u ? gv[t * 9u + k] : 0.f;
+    }
+    __syncthreads();
+    FastBVH f;
+    f.nodes = sn;
+    f.tris = st;
+    return f;
+}
+
+// Per-direction constants parked in the pool (48 bytes).
+struct __align__(16) RayDirRec {
+    float dx, dy, dz, invX;      // invX/Y/Z: the slab-test reciprocals (mesh_bvh.inl:125-135)
+    float invY, invZ, Sx, Sy;    // Woop shear (mesh_bvh.inl:584-741)
+    float Sz;
+    int32_t kperm;               // kx | ky << 2 | kz << 4
+    float a2;                    // dx*dx + dy*dy        (capsule side quadratic)
+    float dd;                    // a2 + dz*dz           (capsule cap quadratic)
+};
+static_assert(sizeof(RayDirRec) == 48, "RayDirRec is 3 x 16 bytes");
+
+__device__ __forceinline__ RayDirRec makeRayDirRec(Vec3 d)
+{
+    constexpr float diveps = 0.0000001f;
+    const Vec3 inv_d = v3(1.f / d.x, 1.f / d.y, 1.f / d.z);
+    const RayTriTxfm tx = computeRayTriTxfm(d, inv_d);
+    RayDirRec r;
+    r.dx = d.x; r.dy = d.y; r.dz = d.z;
+    r.invX = copysignf(d.x == 0 ? 1 / diveps : 1 / d.x, d.x);
+    r.invY = copysignf(d.y == 0 ? 1 / diveps : 1 / d.y, d.y);
+    r.invZ = copysignf(d.z == 0 ? 1 / diveps : 1 / d.z, d.z);
+    r.Sx = tx.Sx; r.Sy = tx.Sy; r.Sz = tx.Sz;
+    r.kperm = tx.kx | (tx.ky << 2) | (tx.kz << 4);
+    r.a2 = d.x * d.x + d.y * d.y;
+    r.dd = r.a2 + d.z * d.z;
+    return r;
+}
+
+// The ray a lane is currently traversing.
+struct RayRegs {
+    float ox, oy, oz;
+    float invX, invY, invZ;
+    float Sx, Sy, Sz;
+    float okx, oky, okz;         // origin permuted by (kx, ky, kz)
+    int32_t kx, ky, kz;
+};
+
+// x, y or z by index, as two SELs (a ?: chain compiles to divergent branches here).
+__device__ __forceinline__ float sel3(int32_t k, float x, float y, float z)
+{
+    float r;
+    asm("{\n\t.reg .pred p0, p1;\n\t"
+        "setp.eq.s32 p0, %1, 0;\n\t"
+        "setp.eq.s32 p1, %1, 1;\n\t"
+        "selp.f32 %0, %3, %4, p1;\n\t"
+        "selp.f32 %0, %2, %0, p0;\n\t}"
+        : "=&f"(r) : "r"(k), "f"(x), "f"(y), "f"(z));
+    return r;
+}
+
+__device__ __forceinline__ void setRay(RayRegs &r, float ox, float oy, float oz, const RayDirRec &d)
+{
+    r.ox = ox; r.oy = oy; r.oz = oz;
+    r.invX = d.invX; r.invY = d.invY; r.invZ = d.invZ;
+    r.Sx = d.Sx; r.Sy = d.Sy; r.Sz = d.Sz;
+    r.kx = d.kperm & 3; r.ky = (d.kperm >> 2) & 3; r.kz = (d.kperm >> 4) & 3;
+    r.okx = sel3(r.kx, ox, oy, oz);
+    r.oky = sel3(r.ky, ox, oy, oz);
+    r.okz = sel3(r.kz, ox, oy, oz);
+}
+
+// rayTriangle of mp_geom.h (mesh_bvh.inl:433-554) on a FastTri; identical
+// arithmetic: comp(tri - org, k) == comp(tri, k) - comp(org, k).
+__device__ __forceinline__ bool rayTriangleFast(const FastTri *tri, const RayRegs &r, float t_max, float *out_t)
+{
+    const float4 q0 = reinterpret_cast<const float4 *>(tri)[0];   // ax ay az bx
+    const float4 q1 = reinterpret_cast<const float4 *>(tri)[1];   // by bz cx cy
+    const float4 q2 = reinterpret_cast<const float4 *>(tri)[2];   // cz
+    const float Akx = sel3(r.kx, q0.x, q0.y, q0.z) - r.okx;
+    const float Aky = sel3(r.ky, q0.x, q0.y, q0.z) - r.oky;
+    const float Akz = sel3(r.kz, q0.x, q0.y, q0.z) - r.okz;
+    const float Bkx = sel3(r.kx, q0.w, q1.x, q1.y) - r.okx;
+    const float Bky = sel3(r.ky, q0.w, q1.x, q1.y) - r.oky;
+    const float Bkz = sel3(r.kz, q0.w, q1.x, q1.y) - r.okz;
+    const float Ckx = sel3(r.kx, q1.z, q1.w, q2.x) - r.okx;
+    const float Cky = sel3(r.ky, q1.z, q1.w, q2.x) - r.oky;
+    const float Ckz = sel3(r.kz, q1.z, q1.w, q2.x) - r.okz;
+
+    const float Ax = fmaf(-r.Sx, Akz, Akx);
+    const float Ay = fmaf(-r.Sy, Akz, Aky);
+    const float Bx = fmaf(-r.Sx, Bkz, Bkx);
+    const float By = fmaf(-r.Sy, Bkz, Bky);
+    const float Cx = fmaf(-r.Sx, Ckz, Ckx);
+    const float Cy = fmaf(-r.Sy, Ckz, Cky);
+
+    float U = fmaf(Cx, By, -Cy * Bx);
+    float V = fmaf(Ax, Cy, -Ay * Cx);
+    float W = fmaf(Bx, Ay, -By * Ax);
+    if (U < 0.0f || V < 0.0f || W < 0.0f) return false;
+    if (U == 0.0f || V == 0.0f || W == 0.0f) {
+        double CxBy = (double)Cx * (double)By;
+        double CyBx = (double)Cy * (double)Bx;
+        U = (float)(CxBy - CyBx);
+        double AxCy = (double)Ax * (double)Cy;
+        double AyCx = (double)Ay * (double)Cx;
+        V = (float)(AxCy - AyCx);
+        double BxAy = (double)Bx * (double)Ay;
+        double ByAx = (double)By * (double)Ax;
+        W = (float)(BxAy - ByAx);
+        if (U < 0.0f || V < 0.0f || W < 0.0f) return false;
+    }
+    const float det = U + V + W;
+    if (det == 0.f) return false;
+    const float Az = r.Sz * Akz, Bz = r.Sz * Bkz, Cz = r.Sz * Ckz;
+    const float T = fmaf(U, Az, fmaf(V, Bz, W * Cz));
+    if (T < 0.0f || T > t_max * det) return false;
+    const float rcpDet = 1.0f / det;
+    *out_t = T * rcpDet;
+    return true;
+}
+
+// One child's slab test against the visit-time constants (mesh_bvh.inl:146-177).
+// Returns t_near, or +inf when the child is absent or its box is missed.
+__device__ __forceinline__ float childNear(const FastChild &c, float dqx, float dqy, float dqz,
+                                           float oqx, float oqy, float oqz)
+{
+    const float t_near_x = c.qMinX * dqx + oqx;
+    const float t_near_y = c.qMinY * dqy + oqy;
+    const float t_near_z = c.qMinZ * dqz + oqz;
+    const float t_far_x = c.qMaxX * dqx + oqx;
+    const float t_far_y = c.qMaxY * dqy + oqy;
+    const float t_far_z = c.qMaxZ * dqz + oqz;
+    const float t_near = fmaxf(fminf(t_near_x, t_far_x), fmaxf(fminf(t_near_y, t_far_y),
+        fmaxf(fminf(t_near_z, t_far_z), 0.f)));
+    const float t_far3 = fminf(fmaxf(t_far_x, t_near_x), fminf(fmaxf(t_far_y, t_near_y),
+        fmaxf(t_far_z, t_near_z)));
+    const bool ok = (c.child != kBVHSentinel) && (t_near <= t_far3);
+    return ok ? t_near : __int_as_float(0x7F800000);
+}
+
+// Pool interface (duck-typed):
+//   int  next()                                  next ray index of this warp's pool, or -1
+//   void load(int ray, RayRegs &r)               fill the lane's registers
+//   void finish(int ray, bool hit, float t)      closest mesh hit of a finished ray
+//
+// Must be entered by all 32 lanes.  A lane with a leaf to test parks until at
+// least kLeafBatch lanes have one (or nobody can advance otherwise), so the
+// triangle block runs with many lanes instead of the two or three that happen
+// to reach a leaf in the same iteration.
+template <int kLeafBatch, class Pool>
+__device__ __forceinline__ void traversePool(const FastBVH &bvh, Pool &pool)
+{
+    int32_t stack[32];
+    int32_t sp = 0;
+    int32_t ray = -1;
+    RayRegs r;
+    float t_max = FLT_MAX;
+    bool hit = false, done = false;
+    // the current node: t_near / child / triSize per slot and the slots still to consider
+    float tn[4] = {0.f, 0.f, 0.f, 0.f};
+    int32_t ch[4] = {0, 0, 0, 0};
+    uint32_t tsz = 0;
+    uint32_t rem = 0;
+    int32_t leaf = -1, ntri = 0;
+
+    for (;;) {
+        if (!done && leaf < 0 && rem == 0) {
+            int32_t node = 0;
+            if (sp == 0) {
+                if (ray >= 0) pool.finish(ray, hit, t_max);
+                ray = pool.next();
+                if (ray < 0) {
+                    done = true;
+                } else {
+                    pool.load(ray, r);
+                    t_max = FLT_MAX;
+                    hit = false;
+                }
+            } else {
+                node = stack[--sp];
+            }
+            if (!done) {
+                const FastNode *nd = bvh.nodes + node;
+                const float4 h0 = reinterpret_cast<const float4 *>(nd)[0];    // minX minY minZ sX
+                const float2 h1 = reinterpret_cast<const float2 *>(nd)[2];    // sY sZ
+                const float dqx = h0.w * r.invX, dqy = h1.x * r.invY, dqz = h1.y * r.invZ;
+                const float oqx = (h0.x - r.ox) * r.invX;
+                const float oqy = (h0.y - r.oy) * r.invY;
+                const float oqz = (h0.z - r.oz) * r.invZ;
+                tsz = 0;
+                rem = 0;
+#pragma unroll
+                for (int i = 0; i < 4; i++) {
+                    const FastChild k = nd->c[i];
+                    tn[i] = childNear(k, dqx, dqy, dqz, oqx, oqy, oqz);
+                    ch[i] = k.child;
+                    tsz |= (uint32_t)k.triSize << (8 * i);
+                    rem |= (tn[i] <= t_max ? 1u : 0u) << i;      // t_max only shrinks: a superset
+                }
+            }
+        }
+        // children in order until a leaf needs testing (internal nodes are pushed);
+        // t_near <= t_max is evaluated at the child's turn, as the reference does
+        if (leaf < 0) {
+#pragma unroll
+            for (int i = 0; i < 4; i++) {
+                const bool turn = leaf < 0 && ((rem >> i) & 1u);
+                if (leaf < 0) rem &= ~(1u << i);
+                if (turn && tn[i] <= t_max) {
+                    if (ch[i] >= 0) {
+                        stack[sp++] = ch[i];
+                    } else {
+                        leaf = ch[i] & 0x7FFFFFFF;
+                        ntri = (int32_t)((tsz >> (8 * i)) & 0xFFu);
+                    }
+                }
+            }
+        }
+        const unsigned pend = __ballot_sync(0xFFFFFFFFu, leaf >= 0);
+        const unsigned can_advance = __ballot_sync(0xFFFFFFFFu, !done && leaf < 0);
+        if (pend == 0 && can_advance == 0) break;
+        if (leaf >= 0 && (__popc(pend) >= kLeafBatch || can_advance == 0)) {
+            // traceRayLeaf (mesh_bvh.inl:360-431): a later triangle replaces an
+            // earlier one whenever T <= t_cur * det.
+            for (int32_t k = 0; k < ntri; k++) {
+                float t;
+                if (rayTriangleFast(bvh.tris + leaf + k, r, t_max, &t)) {
+                    hit = true;
+                    t_max = t;
+                }
+            }
+            leaf = -1;
+        }
+    }
+}
+
+// ---- agent capsules (utils.cpp:39-61 + rayZCapsule of mp_geom.h) -------------
+// Everything of the capsule test that depends on (ray origin, agent) only.
+struct __align__(16) CapsuleRec {
+    float ox, oy, oz, oz1;       // origin relative to the capsule's lower sphere centre; oz1 = oz - h
+    float cCyl, cCap0, cCap1;
+    int32_t inside;              // origin inside the capsule: the test returns "no hit"
+};
+static_assert(sizeof(CapsuleRec) == 32, "CapsuleRec is 2 x 16 bytes");
+
+__device__ __forceinline__ CapsuleRec makeCapsuleRec(Vec3 ray_o, Vec3 agent_pos)
+{
+    const float r = kAgentRadius, h = kStandHeight - 2.f * kAgentRadius;
+    Vec3 capsule_origin = agent_pos;
+    capsule_origin.z += kAgentRadius;
+    const Vec3 o = ray_o - capsule_origin;
+    const float r2 = r * r;
+    CapsuleRec c;
+    c.ox = o.x; c.oy = o.y; c.oz = o.z; c.oz1 = o.z - h;
+    const float zc = fminf(fmaxf(o.z, 0.f), h);
+    const float dz = o.z - zc;
+    const float dist2 = o.x * o.x + o.y * o.y + dz * dz;
+    c.inside = dist2 <= r2 ? 1 : 0;
+    c.cCyl = o.x * o.x + o.y * o.y - r2;
+    c.cCap0 = o.x * o.x + o.y * o.y + o.z * o.z - r2;
+    c.cCap1 = o.x * o.x + o.y * o.y + c.oz1 * c.oz1 - r2;
+    return c;
+}
+
+// rayZCapsule(o, d, 15, 35) with the origin-only terms taken from `c`.  The three
+// discriminants are computed branch-free; the square roots / divisions run only
+// for a ray that can actually touch this capsule.
+__device__ __forceinline__ float rayCapsuleRec(const CapsuleRec &c, float dx, float dy, float dz,
+                                               float a2, float dd)
+{
+    const float h = kStandHeight - 2.f * kAgentRadius;
+    const float bxy = c.ox * dx + c.oy * dy;
+    const float discC = bxy * bxy - a2 * c.cCyl;
+    const float b0 = bxy + c.oz * dz;
+    const float disc0 = b0 * b0 - dd * c.cCap0;
+    const float b1 = bxy + c.oz1 * dz;
+    const float disc1 = b1 * b1 - dd * c.cCap1;
+    const bool side = a2 > 0.f && discC >= 0.f;
+    if (c.inside || !(side || disc0 >= 0.f || disc1 >= 0.f)) return 0.f;
+    float t_hit = FLT_MAX;
+    if (side) {
+        const float t = (-bxy - sqrtf(discC)) / a2;
+        const float z = c.oz + t * dz;
+        if (t > 0.f && z >= 0.f && z <= h) t_hit = t;
+    }
+    if (disc0 >= 0.f) {
+        const float t = (-b0 - sqrtf(disc0)) / dd;
+        if (t > 0.f && t < t_hit) t_hit = t;
+    }
+    if (disc1 >= 0.f) {
+        const float t = (-b1 - sqrtf(disc1)) / dd;
+        if (t > 0.f && t < t_hit) t_hit = t;
+    }
+    return t_hit == FLT_MAX ? 0.f : t_hit;
+}
+
+// The capsule half of traceRayWorld (utils.cpp:39-61): starts from the mesh
+// result and returns the closest hit over the 12 agents of the world.
+__device__ __forceinline__ bool closestWithCapsules(const CapsuleRec *caps, bool mesh_hit, float mesh_t,
+                                                    float dx, float dy, float dz, float a2, float dd,
+                                                    float *t_out, int32_t *agent_out)
+{
+    float min_hit_t = mesh_hit ? mesh_t : FLT_MAX;
+    bool hit = mesh_hit;
+    int32_t hit_agent = -1;
+#pragma unroll
+    for (int i = 0; i < kAgents; i++) {
+        const float t = rayCapsuleRec(caps[i], dx, dy, dz, a2, dd);
+        if (t != 0 && t < min_hit_t) {
+            min_hit_t = t;
+            hit = true;
+            hit_agent = i;
+        }
+    }
+    *t_out = min_hit_t;
+    *agent_out = hit_agent;
+    return hit;
+}
+
+}  // namespace mpenv
