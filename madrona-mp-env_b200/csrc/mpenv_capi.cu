@@ -47,6 +47,9 @@ struct mpenv_handle {
     size_t lidarPoolSmem = 0;
     int gridLidarPool = 0;
     void (*lidarPoolKernel)(KernelArgs) = nullptr;
+    bool poolLos = false;
+    size_t losPoolSmem = 0;
+    int gridLosPool = 0;
     // launch geometry
     int gridMove = 0, gridFire = 0, gridWorld = 0, gridLos = 0, gridObs = 0, gridTeam = 0, gridLidar = 0,
         gridSmall = 0;
@@ -92,12 +95,18 @@ void launchLidar(mpenv_handle *h, cudaStream_t s)
     else k_lidar<<<h->gridLidar, 160, h->bvhSmemBytes, s>>>(h->ka);
 }
 
+void launchLos(mpenv_handle *h, cudaStream_t s)
+{
+    if (h->poolLos) k_los_pool<10, 8><<<h->gridLosPool, kLosWarpsPerCTA * 32, h->losPoolSmem, s>>>(h->ka);
+    else k_los<<<h->gridLos, 128, h->bvhSmemBytes, s>>>(h->ka);
+}
+
 // The obs phase shared by the Init and Step graphs (resetAndObsTasks,
 // sim.cpp:5174-5320): visibility -> masks + observations -> full-team -> lidar.
 uint32_t launchObsPhase(mpenv_handle *h, cudaStream_t s)
 {
     uint32_t n = 0;
-    k_los<<<h->gridLos, 128, h->bvhSmemBytes, s>>>(h->ka); n++;
+    launchLos(h, s); n++;
     k_obs<<<h->gridObs, 128, 0, s>>>(h->ka); n++;
     if (h->fullTeam) { k_fullteam<<<h->gridTeam, 128, 0, s>>>(h->ka); n++; }
     launchLidar(h, s); n++;
@@ -318,12 +327,21 @@ int mpenv_create(const mpenv_config *cfg, mpenv_handle **out)
     const bool legacy = kmode && strcmp(kmode, "legacy") == 0;
     h->lidarPoolSmem = lidarPoolSmemBytes(ka.ctx.bvh.numNodes, ka.ctx.bvh.numTris);
     h->poolLidar = !legacy && h->lidarPoolSmem <= 200 * 1024;
+    h->losPoolSmem = losPoolSmemBytes(ka.ctx.bvh.numNodes, ka.ctx.bvh.numTris);
+    h->poolLos = !legacy && h->losPoolSmem <= 200 * 1024;
+    if (h->poolLos) {
+        MP_CREATE(cudaFuncSetAttribute(k_los_pool<10, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->losPoolSmem));
+        h->gridLosPool = gridFor(h, k_los_pool<10, 8>, kLosWarpsPerCTA * 32, h->losPoolSmem, W * 32);
+    }
     if (h->poolLidar) {
         // leaf-batch threshold of the traversal loop (ray_fast.cuh); tunable for experiments
         const char *lb = getenv("MPENV_LEAF_BATCH");
         const int batch = lb ? atoi(lb) : kLeafBatch;
-        h->lidarPoolKernel = batch <= 1 ? k_lidar_pool<1> : batch <= 6 ? k_lidar_pool<6> :
-                             batch <= 10 ? k_lidar_pool<10> : batch <= 16 ? k_lidar_pool<16> : k_lidar_pool<24>;
+        const char *rb = getenv("MPENV_REFILL_BATCH");
+        const int refill = rb ? atoi(rb) : kRefillBatch;
+        if (refill <= 1) h->lidarPoolKernel = batch <= 1 ? k_lidar_pool<1, 1> : k_lidar_pool<10, 1>;
+        else if (refill <= 4) h->lidarPoolKernel = batch <= 1 ? k_lidar_pool<1, 4> : k_lidar_pool<10, 4>;
+        else h->lidarPoolKernel = batch <= 1 ? k_lidar_pool<1, 8> : k_lidar_pool<10, 8>;
         MP_CREATE(cudaFuncSetAttribute(h->lidarPoolKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->lidarPoolSmem));
         h->gridLidarPool = gridFor(h, h->lidarPoolKernel, kLidarWarpsPerCTA * 32, h->lidarPoolSmem,
                                    (N / 2) * 32);
@@ -569,7 +587,7 @@ int mpenv_step_timed(mpenv_handle *h, float *kernel_ms, const char **kernel_name
     k_move<<<h->gridMove, 128, h->bvhSmemBytes, s>>>(h->ka); names[n++] = "k_move"; cudaEventRecord(ev[n], s);
     k_fire<<<h->gridFire, 128, h->bvhSmemBytes, s>>>(h->ka); names[n++] = "k_fire"; cudaEventRecord(ev[n], s);
     k_world<<<h->gridWorld, 64, 0, s>>>(h->ka); names[n++] = "k_world"; cudaEventRecord(ev[n], s);
-    k_los<<<h->gridLos, 128, h->bvhSmemBytes, s>>>(h->ka); names[n++] = "k_los"; cudaEventRecord(ev[n], s);
+    launchLos(h, s); names[n++] = "k_los"; cudaEventRecord(ev[n], s);
     k_obs<<<h->gridObs, 128, 0, s>>>(h->ka); names[n++] = "k_obs"; cudaEventRecord(ev[n], s);
     if (h->fullTeam) {
         k_fullteam<<<h->gridTeam, 128, 0, s>>>(h->ka); names[n++] = "k_fullteam"; cudaEventRecord(ev[n], s);

@@ -219,17 +219,23 @@ __device__ __forceinline__ float childNear(const FastChild &c, float dqx, float 
 }
 
 // Pool interface (duck-typed):
-//   int  next()                                  next ray index of this warp's pool, or -1
+//   int  count()                                 rays in this warp's pool
 //   void load(int ray, RayRegs &r)               fill the lane's registers
 //   void finish(int ray, bool hit, float t)      closest mesh hit of a finished ray
 //
-// Must be entered by all 32 lanes.  A lane with a leaf to test parks until at
-// least kLeafBatch lanes have one (or nobody can advance otherwise), so the
-// triangle block runs with many lanes instead of the two or three that happen
-// to reach a leaf in the same iteration.
-template <int kLeafBatch, class Pool>
+// Must be entered by all 32 lanes (warp-synchronous: ballots decide the batched
+// steps).  Two things are batched so that their code runs with many lanes
+// instead of the few that happen to need it in a given iteration:
+//   * leaf tests: a lane with a leaf to test parks until kLeafBatch lanes have one;
+//   * ray refill: a lane whose ray is finished parks until kRefillBatch lanes are
+//     idle; ray indices are handed out by ballot rank (no atomics).
+// Either fires at once when no other lane can make progress.
+template <int kLeafBatch, int kRefillBatch, class Pool>
 __device__ __forceinline__ void traversePool(const FastBVH &bvh, Pool &pool)
 {
+    const unsigned lane_lt = (1u << (threadIdx.x & 31)) - 1u;
+    const int32_t pool_count = pool.count();
+    int32_t next_ray = 0;            // warp-uniform
     int32_t stack[32];
     int32_t sp = 0;
     int32_t ray = -1;
@@ -240,65 +246,82 @@ __device__ __forceinline__ void traversePool(const FastBVH &bvh, Pool &pool)
     float tn[4] = {0.f, 0.f, 0.f, 0.f};
     int32_t ch[4] = {0, 0, 0, 0};
     uint32_t tsz = 0;
-    uint32_t rem = 0;
+    uint32_t rem = 0, leafmask = 0;
     int32_t leaf = -1, ntri = 0;
 
     for (;;) {
-        if (!done && leaf < 0 && rem == 0) {
-            int32_t node = 0;
-            if (sp == 0) {
+        const bool idle = !done && leaf < 0 && rem == 0 && sp == 0;
+        const unsigned idle_m = __ballot_sync(0xFFFFFFFFu, idle);
+        const unsigned adv_m = __ballot_sync(0xFFFFFFFFu, !done && !idle && leaf < 0);
+        const unsigned pend_m = __ballot_sync(0xFFFFFFFFu, leaf >= 0);
+        if ((idle_m | adv_m | pend_m) == 0) break;
+        if (idle_m != 0 && (__popc(idle_m) >= kRefillBatch || adv_m == 0)) {
+            if (idle) {
                 if (ray >= 0) pool.finish(ray, hit, t_max);
-                ray = pool.next();
-                if (ray < 0) {
-                    done = true;
-                } else {
+                ray = next_ray + __popc(idle_m & lane_lt);
+                if (ray < pool_count) {
                     pool.load(ray, r);
                     t_max = FLT_MAX;
                     hit = false;
-                }
-            } else {
-                node = stack[--sp];
-            }
-            if (!done) {
-                const FastNode *nd = bvh.nodes + node;
-                const float4 h0 = reinterpret_cast<const float4 *>(nd)[0];    // minX minY minZ sX
-                const float2 h1 = reinterpret_cast<const float2 *>(nd)[2];    // sY sZ
-                const float dqx = h0.w * r.invX, dqy = h1.x * r.invY, dqz = h1.y * r.invZ;
-                const float oqx = (h0.x - r.ox) * r.invX;
-                const float oqy = (h0.y - r.oy) * r.invY;
-                const float oqz = (h0.z - r.oz) * r.invZ;
-                tsz = 0;
-                rem = 0;
-#pragma unroll
-                for (int i = 0; i < 4; i++) {
-                    const FastChild k = nd->c[i];
-                    tn[i] = childNear(k, dqx, dqy, dqz, oqx, oqy, oqz);
-                    ch[i] = k.child;
-                    tsz |= (uint32_t)k.triSize << (8 * i);
-                    rem |= (tn[i] <= t_max ? 1u : 0u) << i;      // t_max only shrinks: a superset
+                    stack[0] = 0;
+                    sp = 1;
+                } else {
+                    ray = -1;
+                    done = true;
                 }
             }
+            next_ray += __popc(idle_m);
         }
-        // children in order until a leaf needs testing (internal nodes are pushed);
-        // t_near <= t_max is evaluated at the child's turn, as the reference does
-        if (leaf < 0) {
+        if (!done && leaf < 0 && rem == 0 && sp > 0) {
+            const int32_t node = stack[--sp];
+            const FastNode *nd = bvh.nodes + node;
+            const float4 h0 = reinterpret_cast<const float4 *>(nd)[0];    // minX minY minZ sX
+            const float2 h1 = reinterpret_cast<const float2 *>(nd)[2];    // sY sZ
+            const float dqx = h0.w * r.invX, dqy = h1.x * r.invY, dqz = h1.y * r.invZ;
+            const float oqx = (h0.x - r.ox) * r.invX;
+            const float oqy = (h0.y - r.oy) * r.invY;
+            const float oqz = (h0.z - r.oz) * r.invZ;
+            tsz = 0;
+            rem = 0;
+            leafmask = 0;
 #pragma unroll
             for (int i = 0; i < 4; i++) {
-                const bool turn = leaf < 0 && ((rem >> i) & 1u);
-                if (leaf < 0) rem &= ~(1u << i);
-                if (turn && tn[i] <= t_max) {
-                    if (ch[i] >= 0) {
-                        stack[sp++] = ch[i];
-                    } else {
-                        leaf = ch[i] & 0x7FFFFFFF;
-                        ntri = (int32_t)((tsz >> (8 * i)) & 0xFFu);
-                    }
-                }
+                const FastChild k = nd->c[i];
+                tn[i] = childNear(k, dqx, dqy, dqz, oqx, oqy, oqz);
+                ch[i] = k.child;
+                tsz |= (uint32_t)k.triSize << (8 * i);
+                rem |= (tn[i] <= t_max ? 1u : 0u) << i;      // t_max only shrinks: a superset
+                leafmask |= (k.child < 0 ? 1u : 0u) << i;
+            }
+        }
+        // Children in order until a leaf needs testing; internal nodes are pushed.
+        // t_near <= t_max is evaluated at the child's turn, as the reference does:
+        // t_max is constant during one scan (only triangle tests change it), so the
+        // four comparisons are taken at once and the in-order walk becomes bit logic.
+        if (leaf < 0 && rem != 0) {
+            uint32_t hits = 0;
+#pragma unroll
+            for (int i = 0; i < 4; i++) hits |= (tn[i] <= t_max ? 1u : 0u) << i;
+            hits &= rem;
+            const uint32_t leaf_hits = hits & leafmask;
+            const int32_t first = leaf_hits ? (__ffs(leaf_hits) - 1) : 4;       // slot of the first leaf hit
+            const uint32_t below = (1u << first) - 1u;
+            const uint32_t push = hits & ~leafmask & below;
+#pragma unroll
+            for (int i = 0; i < 4; i++) {
+                if ((push >> i) & 1u) stack[sp++] = ch[i];
+            }
+            if (first < 4) {
+                const int32_t c = first == 0 ? ch[0] : first == 1 ? ch[1] : first == 2 ? ch[2] : ch[3];
+                leaf = c & 0x7FFFFFFF;
+                ntri = (int32_t)((tsz >> (8 * first)) & 0xFFu);
+                rem &= ~(below | (1u << first));
+            } else {
+                rem = 0;
             }
         }
         const unsigned pend = __ballot_sync(0xFFFFFFFFu, leaf >= 0);
-        const unsigned can_advance = __ballot_sync(0xFFFFFFFFu, !done && leaf < 0);
-        if (pend == 0 && can_advance == 0) break;
+        const unsigned can_advance = __ballot_sync(0xFFFFFFFFu, !done && leaf < 0 && (rem != 0 || sp > 0));
         if (leaf >= 0 && (__popc(pend) >= kLeafBatch || can_advance == 0)) {
             // traceRayLeaf (mesh_bvh.inl:360-431): a later triangle replaces an
             // earlier one whenever T <= t_cur * det.

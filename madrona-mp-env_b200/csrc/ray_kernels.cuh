@@ -19,6 +19,7 @@ constexpr int kLidarWarpsPerCTA = 8;
 #define MPENV_LEAF_BATCH 10
 #endif
 constexpr int kLeafBatch = MPENV_LEAF_BATCH;
+constexpr int kRefillBatch = 8;
 constexpr int kLidarRaysPerAgent = kFwdLidarH * kFwdLidarW + kRearLidarH * kRearLidarW;   // 80
 constexpr int kLidarDirsPerAgent = kFwdLidarW + kRearLidarW;                              // 40
 constexpr int kLidarTaskRays = 2 * kLidarRaysPerAgent;                                    // 160
@@ -45,11 +46,7 @@ __device__ __forceinline__ void lidarDecode(int ray, int *agent, int *rr, int *h
 
 struct LidarPoolAccess {
     LidarWarpPool *P;
-    __device__ __forceinline__ int next()
-    {
-        const int i = atomicAdd(&P->counter, 1);
-        return i < kLidarTaskRays ? i : -1;
-    }
+    __device__ __forceinline__ int count() const { return kLidarTaskRays; }
     __device__ __forceinline__ void load(int ray, RayRegs &r)
     {
         int ag, rr, h, d;
@@ -60,8 +57,8 @@ struct LidarPoolAccess {
     __device__ __forceinline__ void finish(int ray, bool hit, float t) { P->tmesh[ray] = hit ? t : -1.f; }
 };
 
-template <int kBatch>
-__global__ void __launch_bounds__(kLidarWarpsPerCTA * 32) k_lidar_pool(KernelArgs ka)
+template <int kBatch, int kRefill>
+__global__ void __launch_bounds__(kLidarWarpsPerCTA * 32, 3) k_lidar_pool(KernelArgs ka)
 {
     extern __shared__ uint4 smem_raw[];
     const Ctx &c = ka.ctx;
@@ -90,7 +87,6 @@ __global__ void __launch_bounds__(kLidarWarpsPerCTA * 32) k_lidar_pool(KernelArg
             o.z += h_off;
             P.origin[lane] = make_float4(o.x, o.y, o.z, 0.f);
         }
-        if (lane == 0) P.counter = 0;
         for (int d = lane; d < 2 * kLidarDirsPerAgent; d += 32) {
             const int ag = d >= kLidarDirsPerAgent ? 1 : 0;
             const int col = d - ag * kLidarDirsPerAgent;
@@ -113,7 +109,7 @@ __global__ void __launch_bounds__(kLidarWarpsPerCTA * 32) k_lidar_pool(KernelArg
 
         // ---- phase 2: closest mesh hit of the 160 rays
         LidarPoolAccess acc{&P};
-        traversePool<kBatch>(bvh, acc);
+        traversePool<kBatch, kRefill>(bvh, acc);
         __syncwarp();
 
         // ---- phase 3: agent capsules, classification, coalesced export
@@ -144,6 +140,165 @@ __global__ void __launch_bounds__(kLidarWarpsPerCTA * 32) k_lidar_pool(KernelArg
         }
         __syncwarp();
     }
+}
+
+// --------------------------------------------------------------------- LOS
+// opponentsWriteVisibilitySystem (sim.cpp:2526-2560) + isAgentVisible
+// (utils.cpp:186-271).  One warp owns a world: 12 agents x 6 opponents x 4 sample
+// points = 288 candidates.  Most die in the alive / view-space cull; survivors
+// are compacted into the warp's ray pool (ballot rank), traversed with dynamic
+// refill, then checked against the 12 capsules: a sample sees its target iff the
+// closest hit of traceRayAgainstWorld IS the target.  canSee[pair] = OR of its
+// four samples; the order of evaluation is irrelevant (pure per sample).
+constexpr int kLosWarpsPerCTA = 8;
+constexpr int kLosPoolCap = 96;
+constexpr int kLosCandidates = kAgents * kTeamSize * 4;      // 288
+
+struct __align__(16) LosWarpPool {
+    RayDirRec dirs[kLosPoolCap];
+    float4 origin[kAgents];          // eye position of each agent
+    float4 invRot[kAgents];          // inverse aim rotation (x, y, z, w)
+    float4 dRight[kAgents];          // 0.9 r along the observer's right axis
+    float4 target[kAgents];          // position + view height of each agent as a target
+    float tmesh[kLosPoolCap];
+    int32_t meta[kLosPoolCap];       // observer | target << 4 | pair << 8
+    uint32_t seen[4];                // bit per (observer, opponent slot) pair: 72 bits
+    int32_t alive;                   // bit per agent
+    int32_t pad[3];
+};
+
+struct LosPoolAccess {
+    LosWarpPool *P;
+    int32_t n;
+    __device__ __forceinline__ int count() const { return n; }
+    __device__ __forceinline__ void load(int ray, RayRegs &r)
+    {
+        const float4 o = P->origin[P->meta[ray] & 15];
+        setRay(r, o.x, o.y, o.z, P->dirs[ray]);
+    }
+    __device__ __forceinline__ void finish(int ray, bool hit, float t) { P->tmesh[ray] = hit ? t : -1.f; }
+};
+
+template <int kBatch, int kRefill>
+__global__ void __launch_bounds__(kLosWarpsPerCTA * 32, 2) k_los_pool(KernelArgs ka)
+{
+    extern __shared__ uint4 smem_raw[];
+    const Ctx &c = ka.ctx;
+    const FastBVH bvh = stageFastBVH(c.bvh, smem_raw);
+    const size_t bvh_bytes = fastBVHBytes(c.bvh.numNodes, c.bvh.numTris);
+    LosWarpPool *pools = reinterpret_cast<LosWarpPool *>(reinterpret_cast<char *>(smem_raw) + bvh_bytes);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const unsigned lane_lt = (1u << lane) - 1u;
+    LosWarpPool &P = pools[warp];
+    const SimPtrs &p = c.p;
+    const float *fr = c.mc->frustum;
+    const int W = (int)c.cfg.numWorlds;
+
+    for (int w = blockIdx.x * kLosWarpsPerCTA + warp; w < W; w += gridDim.x * kLosWarpsPerCTA) {
+        const int base = w * kAgents;
+        // ---- per-agent terms (utils.cpp:240-251)
+        if (lane < 4) P.seen[lane] = 0;
+        const bool alive_l = lane < kAgents && p.alive[base + lane] != 0.f;
+        const unsigned alive_m = __ballot_sync(0xFFFFFFFFu, alive_l);
+        if (lane < kAgents) {
+            const int idx = base + lane;
+            const Vec3 pos = p.pos[idx];
+            const float vh = viewHeight(p.stand[idx].cur);
+            const Quat rot = p.aim[idx].rot;
+            const Quat inv = quatInv(rot);
+            const Vec3 aim_right = rotateVec(rot, kRight());
+            const Vec3 dr = aim_right * 0.9f * kAgentRadius;
+            P.origin[lane] = make_float4(pos.x, pos.y, pos.z + vh, 0.f);
+            P.invRot[lane] = make_float4(inv.x, inv.y, inv.z, inv.w);
+            P.dRight[lane] = make_float4(dr.x, dr.y, dr.z, 0.f);
+            P.target[lane] = make_float4(pos.x, pos.y, pos.z, vh);
+        }
+        __syncwarp();
+
+        int32_t cand = 0;
+        while (cand < kLosCandidates) {
+            // ---- phase 1: cull candidates, append survivors to the pool
+            int32_t n = 0;
+            while (cand < kLosCandidates && n + 32 <= kLosPoolCap) {
+                const int32_t cd = cand + lane;
+                cand += 32;
+                const int32_t pair = cd >> 2, s = cd & 3;
+                const int32_t a = pair / kTeamSize, j = pair - a * kTeamSize;
+                const int32_t opp = (teamOf(a) ^ 1) * kTeamSize + j;
+                bool ok = ((alive_m >> a) & 1u) && ((alive_m >> opp) & 1u);
+                Vec3 dir = v3(0.f, 1.f, 0.f);
+                if (ok) {
+                    const float4 o4 = P.origin[a], t4 = P.target[opp], q4 = P.invRot[a], r4 = P.dRight[a];
+                    const Vec3 o = v3(o4.x, o4.y, o4.z);
+                    const Vec3 pt = losSamplePoint(v3(t4.x, t4.y, t4.z), t4.w, v3(r4.x, r4.y, r4.z), s);
+                    Quat inv; inv.x = q4.x; inv.y = q4.y; inv.z = q4.z; inv.w = q4.w;
+                    // losSampleVisible up to the ray (utils.cpp:191-219)
+                    Vec3 to_test = pt - o;
+                    const Vec3 vp = rotateVec(inv, to_test);
+                    ok = vp.y > 0.f;
+                    ok = ok && (vp.y * fr[1] - fabsf(vp.x) * fr[0] > -kAgentRadius);
+                    ok = ok && (vp.y * fr[3] - fabsf(vp.z) * fr[2] > -kAgentRadius);
+                    const float len = length(to_test);
+                    ok = ok && !(len < kAgentRadius);
+                    dir = to_test / len;
+                }
+                const unsigned m = __ballot_sync(0xFFFFFFFFu, ok);
+                if (ok) {
+                    const int32_t slot = n + __popc(m & lane_lt);
+                    P.dirs[slot] = makeRayDirRec(dir);
+                    P.meta[slot] = a | (opp << 4) | (pair << 8);
+                }
+                n += __popc(m);
+            }
+            __syncwarp();
+            if (n == 0) continue;
+
+            // ---- phase 2: closest mesh hit
+            LosPoolAccess acc{&P, n};
+            traversePool<kBatch, kRefill>(bvh, acc);
+            __syncwarp();
+
+            // ---- phase 3: capsules; the closest hit must be the target
+            for (int32_t ray = lane; ray < n; ray += 32) {
+                const int32_t meta = P.meta[ray];
+                const int32_t a = meta & 15, opp = (meta >> 4) & 15, pair = meta >> 8;
+                const RayDirRec &dr = P.dirs[ray];
+                const float4 o4 = P.origin[a];
+                const float tm = P.tmesh[ray];
+                float min_hit_t = tm >= 0.f ? tm : FLT_MAX;
+                int32_t hit_agent = -1;
+#pragma unroll 4
+                for (int i = 0; i < kAgents; i++) {
+                    const float4 t4 = P.target[i];
+                    const CapsuleRec cr = makeCapsuleRec(v3(o4.x, o4.y, o4.z), v3(t4.x, t4.y, t4.z));
+                    const float t = rayCapsuleRec(cr, dr.dx, dr.dy, dr.dz, dr.a2, dr.dd);
+                    if (t != 0 && t < min_hit_t) { min_hit_t = t; hit_agent = i; }
+                }
+                if (hit_agent == opp) atomicOr(&P.seen[pair >> 5], 1u << (pair & 31));
+            }
+            __syncwarp();
+        }
+        // ---- export: canSee[agent][8] bytes, 12 agents x 8 B contiguous per world
+        if (lane < kAgents * 2) {
+            const int32_t a = lane >> 1, half = lane & 1;
+            uint32_t word = 0;
+#pragma unroll
+            for (int k = 0; k < 4; k++) {
+                const int32_t j = half * 4 + k;
+                if (j < kTeamSize) {
+                    const int32_t pair = a * kTeamSize + j;
+                    if ((P.seen[pair >> 5] >> (pair & 31)) & 1u) word |= 1u << (8 * k);
+                }
+            }
+            reinterpret_cast<uint32_t *>(p.canSee)[(size_t)base * 2 + lane] = word;
+        }
+        __syncwarp();
+    }
+}
+
+inline size_t losPoolSmemBytes(uint32_t num_nodes, uint32_t num_tris)
+{
+    return fastBVHBytes(num_nodes, num_tris) + kLosWarpsPerCTA * sizeof(LosWarpPool);
 }
 
 inline size_t lidarPoolSmemBytes(uint32_t num_nodes, uint32_t num_tris)
