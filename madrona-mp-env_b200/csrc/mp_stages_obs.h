@@ -165,39 +165,36 @@ MP_HD void fillOtherOb(const SimPtrs &p, OtherPlayerCommonObs &ob, int agent_idx
     ob.relativeFacingPitch = rfp;
 }
 
-// pvpOpponentMasksSystem (sim.cpp:2562-2614) for agent a.
-MP_HD void opponentMasks(const Ctx &c, int w, int a, float *masks_out)
+// pvpOpponentMasksSystem + pvpObservationsSystem (sim.cpp:2645-3052) for agent a,
+// split by output row so that the CUDA kernel can give every row its own thread
+// (12 rows per agent: self, 5 teammates, 6 opponents).  The three parts write
+// disjoint memory and read only state that this stage does not write.
+
+// One opponent-mask entry (sim.cpp:2562-2614).
+MP_HD float opponentMask(const Ctx &c, int w, int a, int i)
 {
     const SimPtrs &p = c.p;
     const int base = w * kAgents;
     const int idx = base + a;
     const int team = teamOf(a);
-    for (int i = 0; i < kTeamSize; i++) {
-        masks_out[i] = 0.f;
-        if (p.alive[idx] == 0.f) continue;
-        const int opp = base + (team ^ 1) * kTeamSize + i;
-        if (p.alive[opp] == 0.f) continue;
-        bool can_see = false;
-        for (int m = 0; m < kTeamSize; m++) {
-            if (p.canSee[(size_t)(base + team * kTeamSize + m) * 8 + i]) { can_see = true; break; }
-        }
-        if (can_see) masks_out[i] = 1.f;
-        if (p.combat[opp].firedShotT >= 0) masks_out[i] = 1.f;
+    if (p.alive[idx] == 0.f) return 0.f;
+    const int opp = base + (team ^ 1) * kTeamSize + i;
+    if (p.alive[opp] == 0.f) return 0.f;
+    float m = 0.f;
+    for (int k = 0; k < kTeamSize; k++) {
+        if (p.canSee[(size_t)(base + team * kTeamSize + k) * 8 + i]) { m = 1.f; break; }
     }
+    if (p.combat[opp].firedShotT >= 0) m = 1.f;
+    return m;
 }
 
-// pvpOpponentMasksSystem + pvpObservationsSystem (sim.cpp:2645-3052), agent a.
-MP_HD void stageObs(const Ctx &c, int w, int a)
+// SelfObservation, SelfPositionObservation, FiltersStateObservation.
+MP_HD void stageObsSelf(const Ctx &c, int w, int a)
 {
     const SimPtrs &p = c.p;
     const MapConsts &mc = *c.mc;
-    const int base = w * kAgents;
-    const int idx = base + a;
+    const int idx = w * kAgents + a;
     const int team = teamOf(a);
-
-    float masks[kTeamSize];
-    opponentMasks(c, w, a, masks);
-    for (int i = 0; i < kTeamSize; i++) p.masks[(size_t)idx * kTeamSize + i] = masks[i];
 
     const WorldState &ws = p.world[w];
     p.filtersObs[idx] = (ws.match.curStep - ws.filtersLastMatchedStep[team] < 5) ? 1.f : 0.f;
@@ -205,31 +202,12 @@ MP_HD void stageObs(const Ctx &c, int w, int a)
     const Vec3 self_pos = p.pos[idx];
     const Aim self_aim = p.aim[idx];
     const Quat self_rot_inv = quatInv(p.rot[idx]);
-    NormPosObs def_pos; def_pos.x = -1000.f; def_pos.y = -1000.f; def_pos.z = -1000.f;
-
     SelfObs self_ob;
     zeroFloats(&self_ob);
-    NormPosObs self_pos_ob = def_pos;
-    bool self_alive = fillCommonOb(c, self_ob, self_pos_ob, idx, self_rot_inv);
-
-    if (!self_alive) {
-        p.selfObs[idx] = self_ob;
-        p.selfPos[idx] = self_pos_ob;
-        TeammateObs tz; zeroFloats(&tz);
-        for (int i = 0; i < kTeamSize - 1; i++) {
-            p.teammateObs[(size_t)idx * (kTeamSize - 1) + i] = tz;
-            p.teammatePos[(size_t)idx * (kTeamSize - 1) + i] = def_pos;
-        }
-        OpponentObs oz; zeroFloats(&oz);
-        for (int i = 0; i < kTeamSize; i++) {
-            p.opponentObs[(size_t)idx * kTeamSize + i] = oz;
-            p.opponentPos[(size_t)idx * kTeamSize + i] = def_pos;
-        }
-        return;
-    }
-
-    fillCombatOb(p, self_ob.combat, idx);
-    {
+    NormPosObs self_pos_ob; self_pos_ob.x = -1000.f; self_pos_ob.y = -1000.f; self_pos_ob.z = -1000.f;
+    const bool self_alive = fillCommonOb(c, self_ob, self_pos_ob, idx, self_rot_inv);
+    if (self_alive) {
+        fillCombatOb(p, self_ob.combat, idx);
         ZoneObs &zo = self_ob.zone;
         const ZoneState &zs = ws.zone;
         AABB zb = mc.zoneBoxes[zs.curZone];
@@ -247,55 +225,91 @@ MP_HD void stageObs(const Ctx &c, int w, int a)
     }
     p.selfObs[idx] = self_ob;
     p.selfPos[idx] = self_pos_ob;
+}
 
-    {
-        int slot = 0;
-        for (int off = 0; off < kTeamSize; off++) {
-            if (off == offsetOf(a)) continue;
-            const int mate = base + team * kTeamSize + off;
-            TeammateObs ob; zeroFloats(&ob);
-            NormPosObs pos_ob = def_pos;
-            if (fillCommonOb(c, ob, pos_ob, mate, self_rot_inv)) {
-                fillOtherOb(p, ob, mate, self_pos, self_aim);
-                fillCombatOb(p, ob.combat, mate);
-            }
-            p.teammateObs[(size_t)idx * (kTeamSize - 1) + slot] = ob;
-            p.teammatePos[(size_t)idx * (kTeamSize - 1) + slot] = pos_ob;
-            slot++;
+// TeammateObservations / TeammatePositionObservations row `slot` (0..4).
+MP_HD void stageObsTeammate(const Ctx &c, int w, int a, int slot)
+{
+    const SimPtrs &p = c.p;
+    const int base = w * kAgents;
+    const int idx = base + a;
+    const int team = teamOf(a);
+    const int off = slot < offsetOf(a) ? slot : slot + 1;       // teammates in offset order, self skipped
+    const int mate = base + team * kTeamSize + off;
+    TeammateObs ob; zeroFloats(&ob);
+    NormPosObs pos_ob; pos_ob.x = -1000.f; pos_ob.y = -1000.f; pos_ob.z = -1000.f;
+    if (p.alive[idx] != 0.f) {
+        const Quat self_rot_inv = quatInv(p.rot[idx]);
+        if (fillCommonOb(c, ob, pos_ob, mate, self_rot_inv)) {
+            fillOtherOb(p, ob, mate, p.pos[idx], p.aim[idx]);
+            fillCombatOb(p, ob.combat, mate);
         }
     }
+    p.teammateObs[(size_t)idx * (kTeamSize - 1) + slot] = ob;
+    p.teammatePos[(size_t)idx * (kTeamSize - 1) + slot] = pos_ob;
+}
 
-    for (int i = 0; i < kTeamSize; i++) {
-        const int opp = base + (team ^ 1) * kTeamSize + i;
-        const size_t row = (size_t)idx * kTeamSize + i;
-        OpponentObs ob; zeroFloats(&ob);
-        NormPosObs pos_ob = def_pos;
-        OpponentObs zero_ob; zeroFloats(&zero_ob);
-        if (!fillCommonOb(c, ob, pos_ob, opp, self_rot_inv)) {
-            p.lastKnownObs[row] = zero_ob;
-            p.lastKnownPos[row] = def_pos;
-            p.opponentObs[row] = ob;
-            p.opponentPos[row] = pos_ob;
-            continue;
-        }
-        fillOtherOb(p, ob, opp, self_pos, self_aim);
-        const CombatState &ocs = p.combat[opp];
-        if (ocs.wasKilled) {
-            p.lastKnownObs[row] = zero_ob;
-            p.lastKnownPos[row] = def_pos;
-        }
-        ob.wasHit = (float)ocs.wasShotCount;
-        ob.firedShot = ocs.firedShotT >= 0.f ? 1.f : 0.f;
-        ob.hasLOS = p.canSee[(size_t)idx * 8 + i] ? 1.f : 0.f;
-        bool team_knows = masks[i] == 1.f;
-        ob.teamKnowsLocation = team_knows ? 1.f : 0.f;
-        if (team_knows) {
-            p.lastKnownObs[row] = ob;
-            p.lastKnownPos[row] = pos_ob;
-        }
+// OpponentObservations / OpponentLastKnownObservations (+ position) row i and
+// OpponentMasks entry i.
+MP_HD void stageObsOpponent(const Ctx &c, int w, int a, int i)
+{
+    const SimPtrs &p = c.p;
+    const int base = w * kAgents;
+    const int idx = base + a;
+    const int team = teamOf(a);
+    const float mask = opponentMask(c, w, a, i);
+    p.masks[(size_t)idx * kTeamSize + i] = mask;
+
+    const int opp = base + (team ^ 1) * kTeamSize + i;
+    const size_t row = (size_t)idx * kTeamSize + i;
+    NormPosObs def_pos; def_pos.x = -1000.f; def_pos.y = -1000.f; def_pos.z = -1000.f;
+    OpponentObs ob; zeroFloats(&ob);
+    NormPosObs pos_ob = def_pos;
+    if (p.alive[idx] == 0.f) {          // dead observer: zero rows, last-known rows untouched
+        p.opponentObs[row] = ob;
+        p.opponentPos[row] = def_pos;
+        return;
+    }
+    const Quat self_rot_inv = quatInv(p.rot[idx]);
+    OpponentObs zero_ob; zeroFloats(&zero_ob);
+    if (!fillCommonOb(c, ob, pos_ob, opp, self_rot_inv)) {
+        p.lastKnownObs[row] = zero_ob;
+        p.lastKnownPos[row] = def_pos;
         p.opponentObs[row] = ob;
         p.opponentPos[row] = pos_ob;
+        return;
     }
+    fillOtherOb(p, ob, opp, p.pos[idx], p.aim[idx]);
+    const CombatState &ocs = p.combat[opp];
+    if (ocs.wasKilled) {
+        p.lastKnownObs[row] = zero_ob;
+        p.lastKnownPos[row] = def_pos;
+    }
+    ob.wasHit = (float)ocs.wasShotCount;
+    ob.firedShot = ocs.firedShotT >= 0.f ? 1.f : 0.f;
+    ob.hasLOS = p.canSee[(size_t)idx * 8 + i] ? 1.f : 0.f;
+    const bool team_knows = mask == 1.f;
+    ob.teamKnowsLocation = team_knows ? 1.f : 0.f;
+    if (team_knows) {
+        p.lastKnownObs[row] = ob;
+        p.lastKnownPos[row] = pos_ob;
+    }
+    p.opponentObs[row] = ob;
+    p.opponentPos[row] = pos_ob;
+}
+
+// Row r of agent a: 0 = self, 1..5 = teammates, 6..11 = opponents.
+constexpr int kObsRowsPerAgent = 2 * kTeamSize;
+MP_HD void stageObsRow(const Ctx &c, int w, int a, int r)
+{
+    if (r == 0) stageObsSelf(c, w, a);
+    else if (r < kTeamSize) stageObsTeammate(c, w, a, r - 1);
+    else stageObsOpponent(c, w, a, r - kTeamSize);
+}
+
+MP_HD void stageObs(const Ctx &c, int w, int a)
+{
+    for (int r = 0; r < kObsRowsPerAgent; r++) stageObsRow(c, w, a, r);
 }
 
 // fullTeamObservationsSystem (sim.cpp:3054-3301) for team t of world w.  Runs

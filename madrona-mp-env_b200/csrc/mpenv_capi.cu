@@ -317,7 +317,7 @@ int mpenv_create(const mpenv_config *cfg, mpenv_handle **out)
     h->gridFire = gridFor(h, k_fire, 128, h->bvhSmemBytes, N);
     h->gridWorld = gridFor(h, k_world, 64, 0, W);
     h->gridLos = gridFor(h, k_los, 128, h->bvhSmemBytes, N * kTeamSize);
-    h->gridObs = gridFor(h, k_obs, 128, 0, N);
+    h->gridObs = gridFor(h, k_obs, 128, 0, N * kObsRowsPerAgent);
     h->gridTeam = gridFor(h, k_fullteam, 128, 0, W * 2);
     h->gridLidar = gridFor(h, k_lidar, 160, h->bvhSmemBytes, N * 80);
     h->gridSmall = gridFor(h, k_reset, 128, 0, W);

@@ -118,13 +118,18 @@ __global__ void __launch_bounds__(128) k_los(KernelArgs ka)
     }
 }
 
+// One thread per output ROW (12 per agent: self, 5 teammates, 6 opponents): 12x the
+// parallelism of a thread per agent, and consecutive lanes write consecutive
+// 128-byte rows of the same tensor.
 __global__ void __launch_bounds__(128) k_obs(KernelArgs ka)
 {
     const Ctx &c = ka.ctx;
-    const int N = (int)c.cfg.numWorlds * kAgents;
-    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < N; i += gridDim.x * blockDim.x) {
+    const long long R = (long long)c.cfg.numWorlds * kAgents * kObsRowsPerAgent;
+    for (long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x; g < R;
+         g += (long long)gridDim.x * blockDim.x) {
+        const int i = (int)(g / kObsRowsPerAgent), r = (int)(g - (long long)i * kObsRowsPerAgent);
         const int w = i / kAgents, a = i - w * kAgents;
-        stageObs(c, w, a);
+        stageObsRow(c, w, a, r);
     }
 }
 
