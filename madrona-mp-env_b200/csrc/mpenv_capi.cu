@@ -30,6 +30,10 @@ struct mpenv_handle {
     int device = 0;
     int numSMs = 0;
     cudaStream_t stream = nullptr;
+    cudaStream_t sideStream = nullptr;       // capture-time fork of the obs phase
+    cudaEvent_t evFork = nullptr, evJoin = nullptr;
+    bool forkObs = false;                    // measured slower on B200 (3.17 vs 3.02 ms/step): the
+                                             // persistent lidar grid already fills every SM
     MapAssets assets;
     MapConsts hostConsts;
     MapConsts *devConsts = nullptr;
@@ -103,32 +107,56 @@ void launchLos(mpenv_handle *h, cudaStream_t s)
 
 // The obs phase shared by the Init and Step graphs (resetAndObsTasks,
 // sim.cpp:5174-5320): visibility -> masks + observations -> full-team -> lidar.
-uint32_t launchObsPhase(mpenv_handle *h, cudaStream_t s)
+uint32_t launchObsPhase(mpenv_handle *h, cudaStream_t s, bool fork)
 {
     uint32_t n = 0;
-    launchLos(h, s); n++;
-    k_obs<<<h->gridObs, 128, 0, s>>>(h->ka); n++;
-    if (h->fullTeam) { k_fullteam<<<h->gridTeam, 128, 0, s>>>(h->ka); n++; }
-    launchLidar(h, s); n++;
+    if (!fork) {
+        launchLos(h, s); n++;
+        k_obs<<<h->gridObs, 128, 0, s>>>(h->ka); n++;
+        if (h->fullTeam) { k_fullteam<<<h->gridTeam, 128, 0, s>>>(h->ka); n++; }
+        launchLidar(h, s); n++;
+        return n;
+    }
+    // Graph capture: the lidar kernel (issue bound, reads pos / aim / rot / stand only)
+    // runs beside visibility -> observation packing (latency / HBM bound).  With the
+    // full-team tensors the side branch starts after visibility, because
+    // k_fullteam reads canSee and must see the PREVIOUS step's lidar.
+    cudaStream_t side = h->sideStream;
+    if (!h->fullTeam) {
+        cudaEventRecord(h->evFork, s);
+        cudaStreamWaitEvent(side, h->evFork, 0);
+        launchLidar(h, side); n++;
+        launchLos(h, s); n++;
+        k_obs<<<h->gridObs, 128, 0, s>>>(h->ka); n++;
+    } else {
+        launchLos(h, s); n++;
+        cudaEventRecord(h->evFork, s);
+        cudaStreamWaitEvent(side, h->evFork, 0);
+        k_fullteam<<<h->gridTeam, 128, 0, side>>>(h->ka); n++;
+        launchLidar(h, side); n++;
+        k_obs<<<h->gridObs, 128, 0, s>>>(h->ka); n++;
+    }
+    cudaEventRecord(h->evJoin, side);
+    cudaStreamWaitEvent(s, h->evJoin, 0);
     return n;
 }
 
-uint32_t launchStep(mpenv_handle *h, cudaStream_t s)
+uint32_t launchStep(mpenv_handle *h, cudaStream_t s, bool fork)
 {
     uint32_t n = 0;
     k_move<<<h->gridMove, 128, h->bvhSmemBytes, s>>>(h->ka); n++;
     k_fire<<<h->gridFire, 128, h->bvhSmemBytes, s>>>(h->ka); n++;
     k_world<<<h->gridWorld, 64, 0, s>>>(h->ka); n++;
-    n += launchObsPhase(h, s);
+    n += launchObsPhase(h, s, fork);
     return n;
 }
 
-uint32_t launchInit(mpenv_handle *h, cudaStream_t s)
+uint32_t launchInit(mpenv_handle *h, cudaStream_t s, bool fork)
 {
     uint32_t n = 0;
     k_force_reset<<<h->gridSmall, 128, 0, s>>>(h->ka); n++;
     k_reset<<<h->gridSmall, 128, 0, s>>>(h->ka); n++;
-    n += launchObsPhase(h, s);
+    n += launchObsPhase(h, s, fork);
     return n;
 }
 
@@ -136,7 +164,7 @@ int captureGraph(mpenv_handle *h, bool step, cudaGraphExec_t *out, uint32_t *lau
 {
     cudaGraph_t graph = nullptr;
     MP_CUDA(h, cudaStreamBeginCapture(h->stream, cudaStreamCaptureModeThreadLocal));
-    *launches = step ? launchStep(h, h->stream) : launchInit(h, h->stream);
+    *launches = step ? launchStep(h, h->stream, h->forkObs) : launchInit(h, h->stream, h->forkObs);
     MP_CUDA(h, cudaStreamEndCapture(h->stream, &graph));
     MP_CUDA(h, cudaGraphInstantiate(out, graph, 0));
     MP_CUDA(h, cudaGraphDestroy(graph));
@@ -211,6 +239,9 @@ void mpenv_destroy(mpenv_handle *h)
     if (h->stepGraph) cudaGraphExecDestroy(h->stepGraph);
     if (h->initGraph) cudaGraphExecDestroy(h->initGraph);
     for (void *p : h->allocs) cudaFree(p);
+    if (h->evFork) cudaEventDestroy(h->evFork);
+    if (h->evJoin) cudaEventDestroy(h->evJoin);
+    if (h->sideStream) cudaStreamDestroy(h->sideStream);
     if (h->stream) cudaStreamDestroy(h->stream);
     delete h;
 }
@@ -253,6 +284,10 @@ int mpenv_create(const mpenv_config *cfg, mpenv_handle **out)
     MP_CREATE(cudaGetDeviceProperties(&prop, h->device));
     h->numSMs = prop.multiProcessorCount;
     MP_CREATE(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
+    MP_CREATE(cudaStreamCreateWithFlags(&h->sideStream, cudaStreamNonBlocking));
+    MP_CREATE(cudaEventCreateWithFlags(&h->evFork, cudaEventDisableTiming));
+    MP_CREATE(cudaEventCreateWithFlags(&h->evJoin, cudaEventDisableTiming));
+    { const char *f = getenv("MPENV_FORK_OBS"); h->forkObs = f && f[0] == '1'; }
 
     auto devAlloc = [&](void **ptr, size_t bytes) -> bool {
         if (!cudaOk(h, cudaMalloc(ptr, bytes), "cudaMalloc")) return false;
