@@ -163,9 +163,15 @@ def run_ours(args):
     dom = max(acc, key=acc.get)
     peak, peak_src = peaks()
     achieved = KERNEL_BYTES[dom] * N / (acc[dom] * 1e-3) / 1e9
+    traffic = None
+    tpath = os.path.join(ROOT, "profiles", "ncu_traffic.json")
+    if os.path.exists(tpath):
+        tj = json.load(open(tpath))
+        if tj.get("worlds") == W:
+            traffic = tj["bytes_per_launch"].get(dom)
     roofline = {"bound": "hbm", "kernel": dom, "achieved": round(achieved, 2), "peak": peak,
                 "peak_source": peak_src, "unit": "GB/s", "frac": round(achieved / peak, 5),
-                "traffic": None, "kernel_ms": {k: round(v, 4) for k, v in acc.items()},
+                "traffic": traffic, "algorithmic_bytes_per_launch": KERNEL_BYTES[dom] * N, "kernel_ms": {k: round(v, 4) for k, v in acc.items()},
                 "bytes_per_agent_step": KERNEL_BYTES[dom]}
 
     # ---- e2e: C ABI with HOST buffers, copies inside the timed region --------
