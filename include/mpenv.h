@@ -128,6 +128,8 @@ int mpenv_step_async(mpenv_handle *h, void *cuda_stream);
  * outputs back, all on `cuda_stream`.  Buffer order = mpenv_train_interface(). */
 int mpenv_stream_init(mpenv_handle *h, void *cuda_stream, void **buffers);
 int mpenv_stream_step(mpenv_handle *h, void *cuda_stream, void **buffers);
+/* The handle's own cudaStream_t (the stream of mpenv_step / the *_tensor_async copies). */
+void *mpenv_stream(mpenv_handle *h);
 /* Waits for the handle's own stream. */
 int mpenv_sync(mpenv_handle *h);
 /* Manager::*Tensor() exporters (mgr.cpp:1965-2381). */
@@ -140,6 +142,15 @@ int mpenv_tensor(mpenv_handle *h, uint32_t export_id, mpenv_tensor_desc *out);
  * memory from mpenv_host_alloc makes the copies truly asynchronous. */
 int mpenv_write_tensor_async(mpenv_handle *h, uint32_t export_id, const void *host_src, uint64_t bytes);
 int mpenv_read_tensor_async(mpenv_handle *h, uint32_t export_id, void *host_dst, uint64_t bytes);
+/* Pipelined read-back for host consumers: snapshots the `n` listed tensors
+ * device->device on the handle's stream (ordered after the step that produced
+ * them, so the NEXT step may overwrite the live tensors), then copies the
+ * snapshot device->host on a second stream, overlapping the next step's
+ * kernels with the PCIe transfer.  host_dst[i] must stay valid until
+ * mpenv_read_wait() returns; a new call first waits (stream-ordered) for the
+ * previous transfer.  Pinned host memory required for real overlap. */
+int mpenv_read_tensors_pipelined(mpenv_handle *h, const uint32_t *export_ids, void *const *host_dst, uint32_t n);
+int mpenv_read_wait(mpenv_handle *h);
 int mpenv_host_alloc(uint64_t bytes, void **out);
 void mpenv_host_free(void *p);
 

@@ -47,6 +47,12 @@ struct mpenv_handle {
     cudaGraphExec_t stepGraph = nullptr;
     cudaGraphExec_t initGraph = nullptr;
     bool fullTeam = false;
+    // pipelined host read-back (mpenv_read_tensors_pipelined)
+    cudaStream_t copyStream = nullptr;
+    cudaEvent_t evSnap = nullptr, evCopied = nullptr;
+    char *snapshot = nullptr;
+    size_t snapshotBytes = 0;
+    bool copyInFlight = false;
     bool poolLidar = false;                  // warp-pooled ray engine (ray_kernels.cuh)
     size_t lidarPoolSmem = 0;
     int gridLidarPool = 0;
@@ -239,6 +245,10 @@ void mpenv_destroy(mpenv_handle *h)
     if (h->stepGraph) cudaGraphExecDestroy(h->stepGraph);
     if (h->initGraph) cudaGraphExecDestroy(h->initGraph);
     for (void *p : h->allocs) cudaFree(p);
+    if (h->copyStream) { cudaStreamSynchronize(h->copyStream); cudaStreamDestroy(h->copyStream); }
+    if (h->evSnap) cudaEventDestroy(h->evSnap);
+    if (h->evCopied) cudaEventDestroy(h->evCopied);
+    if (h->snapshot) cudaFree(h->snapshot);
     if (h->evFork) cudaEventDestroy(h->evFork);
     if (h->evJoin) cudaEventDestroy(h->evJoin);
     if (h->sideStream) cudaStreamDestroy(h->sideStream);
@@ -411,6 +421,8 @@ int mpenv_step_async(mpenv_handle *h, void *cuda_stream)
     return MPENV_OK;
 }
 
+void *mpenv_stream(mpenv_handle *h) { return h ? (void *)h->stream : nullptr; }
+
 int mpenv_sync(mpenv_handle *h)
 {
     if (!h) return MPENV_ERR_INVALID;
@@ -498,6 +510,58 @@ int mpenv_read_tensor_async(mpenv_handle *h, uint32_t export_id, void *host_dst,
     if (bytes != tensorBytes(d)) return fail(h, MPENV_ERR_INVALID, "mpenv_read_tensor_async: size mismatch");
     MP_CUDA(h, cudaSetDevice(h->device));
     MP_CUDA(h, cudaMemcpyAsync(host_dst, d.dev_ptr, bytes, cudaMemcpyDeviceToHost, h->stream));
+    return MPENV_OK;
+}
+
+int mpenv_read_tensors_pipelined(mpenv_handle *h, const uint32_t *export_ids, void *const *host_dst, uint32_t n)
+{
+    if (!h || !export_ids || !host_dst || n == 0 || n > 64) return MPENV_ERR_INVALID;
+    MP_CUDA(h, cudaSetDevice(h->device));
+    mpenv_tensor_desc d[64];
+    size_t total = 0;
+    for (uint32_t i = 0; i < n; i++) {
+        int rc = mpenv_tensor(h, export_ids[i], &d[i]);
+        if (rc != MPENV_OK) return rc;
+        if (!host_dst[i]) return fail(h, MPENV_ERR_INVALID, "mpenv_read_tensors_pipelined: null host buffer");
+        total += (tensorBytes(d[i]) + 255) & ~(size_t)255;
+    }
+    if (!h->copyStream) {
+        MP_CUDA(h, cudaStreamCreateWithFlags(&h->copyStream, cudaStreamNonBlocking));
+        MP_CUDA(h, cudaEventCreateWithFlags(&h->evSnap, cudaEventDisableTiming));
+        MP_CUDA(h, cudaEventCreateWithFlags(&h->evCopied, cudaEventDisableTiming));
+    }
+    if (total > h->snapshotBytes) {
+        MP_CUDA(h, cudaStreamSynchronize(h->copyStream));
+        if (h->snapshot) cudaFree(h->snapshot);
+        h->snapshot = nullptr; h->snapshotBytes = 0;
+        MP_CUDA(h, cudaMalloc((void **)&h->snapshot, total));
+        h->snapshotBytes = total;
+    }
+    // the snapshot may not be overwritten before the previous transfer has left it
+    if (h->copyInFlight) MP_CUDA(h, cudaStreamWaitEvent(h->stream, h->evCopied, 0));
+    size_t off = 0;
+    for (uint32_t i = 0; i < n; i++) {
+        MP_CUDA(h, cudaMemcpyAsync(h->snapshot + off, d[i].dev_ptr, tensorBytes(d[i]), cudaMemcpyDeviceToDevice, h->stream));
+        off += (tensorBytes(d[i]) + 255) & ~(size_t)255;
+    }
+    MP_CUDA(h, cudaEventRecord(h->evSnap, h->stream));
+    MP_CUDA(h, cudaStreamWaitEvent(h->copyStream, h->evSnap, 0));
+    off = 0;
+    for (uint32_t i = 0; i < n; i++) {
+        MP_CUDA(h, cudaMemcpyAsync(host_dst[i], h->snapshot + off, tensorBytes(d[i]), cudaMemcpyDeviceToHost, h->copyStream));
+        off += (tensorBytes(d[i]) + 255) & ~(size_t)255;
+    }
+    MP_CUDA(h, cudaEventRecord(h->evCopied, h->copyStream));
+    h->copyInFlight = true;
+    return MPENV_OK;
+}
+
+int mpenv_read_wait(mpenv_handle *h)
+{
+    if (!h) return MPENV_ERR_INVALID;
+    if (!h->copyInFlight) return MPENV_OK;
+    MP_CUDA(h, cudaSetDevice(h->device));
+    MP_CUDA(h, cudaEventSynchronize(h->evCopied));
     return MPENV_OK;
 }
 

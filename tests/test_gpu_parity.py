@@ -231,3 +231,39 @@ def test_python_manager_zero_copy_and_stream_step():
     finally:
         orc.close()
         del mgr
+
+
+def test_pipelined_readback_equals_sync_read():
+    """mpenv_read_tensors_pipelined: the snapshot taken after step t must survive step t+1."""
+    import ctypes as C
+    W = 16
+    a_, b_ = S.GpuSim(W, auto_reset=True), S.GpuSim(W, auto_reset=True)
+    try:
+        L, h = a_.lib, a_.h
+        L.mpenv_read_tensors_pipelined.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32]
+        L.mpenv_read_wait.argtypes = [C.c_void_p]
+        L.mpenv_stream.restype = C.c_void_p
+        L.mpenv_stream.argtypes = [C.c_void_p]
+        names = ["self_obs", "fwd_lidar", "opponent_last_known_obs", "reward", "match_result"]
+        bufs = {n: np.zeros((S.rows_of(S.EXPORT_SHAPES[n][0], W), S.EXPORT_SHAPES[n][1]), S.EXPORT_SHAPES[n][2])
+                for n in names}
+        ids = (C.c_uint32 * len(names))(*[S.EXPORT_IDS[n] for n in names])
+        dst = (C.c_void_p * len(names))(*[bufs[n].ctypes.data for n in names])
+        a_.init(); b_.init()
+        prev = None
+        for s in range(12):
+            d, act = S.seek_policy(b_, s, W)
+            a_.set_actions(d, act); b_.set_actions(d, act)
+            assert L.mpenv_step_async(h, C.c_void_p(L.mpenv_stream(h))) == 0
+            assert L.mpenv_read_wait(h) == 0
+            if prev is not None:          # host buffers now hold step s-1, although step s is already queued
+                for n in names:
+                    assert np.array_equal(bufs[n].view(np.int32), prev[n].view(np.int32)), (s, n)
+            assert L.mpenv_read_tensors_pipelined(h, ids, dst, len(names)) == 0
+            b_.step()
+            prev = {n: b_.export(n) for n in names}
+        assert L.mpenv_read_wait(h) == 0
+        for n in names:
+            assert np.array_equal(bufs[n].view(np.int32), prev[n].view(np.int32)), n
+    finally:
+        a_.close(); b_.close()
