@@ -152,7 +152,7 @@ uint32_t launchStep(mpenv_handle *h, cudaStream_t s, bool fork)
     uint32_t n = 0;
     k_move<<<h->gridMove, 128, h->bvhSmemBytes, s>>>(h->ka); n++;
     k_fire<<<h->gridFire, 128, h->bvhSmemBytes, s>>>(h->ka); n++;
-    k_world<<<h->gridWorld, 64, 0, s>>>(h->ka); n++;
+    k_world<<<h->gridWorld, 128, 0, s>>>(h->ka); n++;
     n += launchObsPhase(h, s, fork);
     return n;
 }
@@ -360,7 +360,7 @@ int mpenv_create(const mpenv_config *cfg, mpenv_handle **out)
     const long long W = cfg->num_worlds, N = W * kAgents;
     h->gridMove = gridFor(h, k_move, 128, h->bvhSmemBytes, N);
     h->gridFire = gridFor(h, k_fire, 128, h->bvhSmemBytes, N);
-    h->gridWorld = gridFor(h, k_world, 64, 0, W);
+    h->gridWorld = gridFor(h, k_world, 128, 0, W * 16);
     h->gridLos = gridFor(h, k_los, 128, h->bvhSmemBytes, N * kTeamSize);
     h->gridObs = gridFor(h, k_obs, 128, 0, N * kObsRowsPerAgent);
     h->gridTeam = gridFor(h, k_fullteam, 128, 0, W * 2);
@@ -685,7 +685,7 @@ int mpenv_step_timed(mpenv_handle *h, float *kernel_ms, const char **kernel_name
     MP_CUDA(h, cudaEventRecord(ev[0], s));
     k_move<<<h->gridMove, 128, h->bvhSmemBytes, s>>>(h->ka); names[n++] = "k_move"; cudaEventRecord(ev[n], s);
     k_fire<<<h->gridFire, 128, h->bvhSmemBytes, s>>>(h->ka); names[n++] = "k_fire"; cudaEventRecord(ev[n], s);
-    k_world<<<h->gridWorld, 64, 0, s>>>(h->ka); names[n++] = "k_world"; cudaEventRecord(ev[n], s);
+    k_world<<<h->gridWorld, 128, 0, s>>>(h->ka); names[n++] = "k_world"; cudaEventRecord(ev[n], s);
     launchLos(h, s); names[n++] = "k_los"; cudaEventRecord(ev[n], s);
     k_obs<<<h->gridObs, 128, 0, s>>>(h->ka); names[n++] = "k_obs"; cudaEventRecord(ev[n], s);
     if (h->fullTeam) {

@@ -98,11 +98,62 @@ __global__ void __launch_bounds__(128) k_fire(KernelArgs ka)
     }
 }
 
-__global__ void __launch_bounds__(64) k_world(KernelArgs ka)
+// stageWorld (mp_stages_world.h) executed by a 16-lane group per world: the
+// per-agent systems (damage, autoheal, explore grid, zone reward) run on lanes
+// 0..11 in parallel -- each touches only its own agent's rows -- and the systems
+// with sequential-in-world semantics (respawn draw order, zone state machine,
+// breadcrumb pool order, match info, team reward, reset) run on lane 0, in task
+// graph order (sim.cpp:5508-5842).  __syncwarp() orders the phases' global-memory
+// traffic.  16x the threads of a thread-per-world launch: latency is what bounds
+// this stage.
+__global__ void __launch_bounds__(128) k_world(KernelArgs ka)
 {
-    const int W = (int)ka.ctx.cfg.numWorlds;
-    for (int w = blockIdx.x * blockDim.x + threadIdx.x; w < W; w += gridDim.x * blockDim.x)
-        stageWorld(ka.ctx, w);
+    const Ctx &c = ka.ctx;
+    const SimPtrs &p = c.p;
+    const int W = (int)c.cfg.numWorlds;
+    const int lane = threadIdx.x & 15;
+    const int half = (threadIdx.x >> 4) & 1;
+    const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int num_warps = (gridDim.x * blockDim.x) >> 5;
+    for (int wp = warp; wp * 2 < W; wp += num_warps) {
+        const int w = wp * 2 + half;
+        const bool valid = w < W;
+        const int base = w * kAgents;
+        const bool agent = valid && lane < kAgents;
+        const bool lead = valid && lane == 0;
+        if (agent) applyDmgSystem(p, base + lane);
+        __syncwarp();
+        if (lead && !(c.cfg.simFlags & kFlagNoRespawn)) spawnAgents(c, w, true);
+        __syncwarp();
+        if (agent) autoHealSystem(p, base + lane);
+        __syncwarp();
+        if (lead) {
+            zoneSystem(c, w);
+            breadcrumbSystems(c, w);
+            zoneMatchInfoSystem(c, w);
+            evaluateGoalRegionsSystem(c, w);
+        }
+        __syncwarp();
+        if (agent) {
+            exploreVisitedSystem(c, w, base + lane);
+            zoneRewardSystem(c, w, lane);
+        }
+        __syncwarp();
+        if (lead) {
+            teamAndFinalReward(c, w);
+            const int32_t finished = p.world[w].match.isFinished;
+            for (int i = 0; i < kAgents; i++) p.done[base + i] = finished;
+            // fullTeamDoneRewardSystem (sim.cpp:4720-4748)
+            for (int t = 0; t < 2; t++) {
+                float r = 0.f;
+                for (int i = 0; i < kTeamSize; i++) r += p.reward[base + t * kTeamSize + i];
+                p.ftReward[w * 2 + t] = r;
+                p.ftDone[w * 2 + t] = finished ? 1 : 0;
+            }
+            resetSystem(c, w);
+        }
+        __syncwarp();
+    }
 }
 
 __global__ void __launch_bounds__(128) k_los(KernelArgs ka)
