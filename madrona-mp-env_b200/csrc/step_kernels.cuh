@@ -21,6 +21,7 @@
 #include <cuda_runtime.h>
 
 #include "mp_stages.h"
+#include "world_coop.cuh"
 
 namespace mpenv {
 
@@ -127,13 +128,11 @@ __global__ void __launch_bounds__(128) k_world(KernelArgs ka)
         __syncwarp();
         if (agent) autoHealSystem(p, base + lane);
         __syncwarp();
-        if (lead) {
-            zoneSystem(c, w);
-            breadcrumbSystems(c, w);
-            zoneMatchInfoSystem(c, w);
-            evaluateGoalRegionsSystem(c, w);
-        }
+        zoneSystemCoop(c, w, lane, half, valid);
+        breadcrumbSystemsCoop(c, w, lane, half, valid);
+        if (lead) zoneMatchInfoSystem(c, w);
         __syncwarp();
+        evaluateGoalRegionsCoop(c, w, lane, half, valid);
         if (agent) {
             exploreVisitedSystem(c, w, base + lane);
             zoneRewardSystem(c, w, lane);
