@@ -123,6 +123,7 @@ struct RayRegs {
     float Sx, Sy, Sz;
     float okx, oky, okz;         // origin permuted by (kx, ky, kz)
     int32_t kx, ky, kz;
+    float tStop;                 // any-hit threshold: the ray ends at an accepted hit with t <= tStop
 };
 
 // x, y or z by index, as two SELs (a ?: chain compiles to divergent branches here).
@@ -333,6 +334,7 @@ __device__ __forceinline__ void traversePool(const FastBVH &bvh, Pool &pool)
                 }
             }
             leaf = -1;
+            if (hit && t_max <= r.tStop) { sp = 0; rem = 0; }     // occluder found: this ray is done
         }
     }
 }

@@ -53,6 +53,7 @@ struct LidarPoolAccess {
         lidarDecode(ray, &ag, &rr, &h, &d);
         const float4 o = P->origin[ag * 2 + h];
         setRay(r, o.x, o.y, o.z, P->dirs[d]);
+        r.tStop = -1.f;                  // closest hit wanted: never stop early
     }
     __device__ __forceinline__ void finish(int ray, bool hit, float t) { P->tmesh[ray] = hit ? t : -1.f; }
 };
@@ -147,9 +148,12 @@ __global__ void __launch_bounds__(kLidarWarpsPerCTA * 32, 3) k_lidar_pool(Kernel
 // (utils.cpp:186-271).  One warp owns a world: 12 agents x 6 opponents x 4 sample
 // points = 288 candidates.  Most die in the alive / view-space cull; survivors
 // are compacted into the warp's ray pool (ballot rank), traversed with dynamic
-// refill, then checked against the 12 capsules: a sample sees its target iff the
-// closest hit of traceRayAgainstWorld IS the target.  canSee[pair] = OR of its
-// four samples; the order of evaluation is irrelevant (pure per sample).
+// refill.  A sample sees its target iff the closest hit of traceRayAgainstWorld
+// IS the target; that is decided exactly without finishing every traversal:
+// the capsule tests run first (target must win among the capsules), and a ray
+// stops at the first ACCEPTED mesh hit with t <= t_target -- accepted hits only
+// decrease, so such a hit exists iff the final closest mesh hit is <= t_target.
+// canSee[pair] = OR of its four samples (pure per sample, order irrelevant).
 constexpr int kLosWarpsPerCTA = 8;
 constexpr int kLosPoolCap = 96;
 constexpr int kLosCandidates = kAgents * kTeamSize * 4;      // 288
@@ -161,6 +165,7 @@ struct __align__(16) LosWarpPool {
     float4 dRight[kAgents];          // 0.9 r along the observer's right axis
     float4 target[kAgents];          // position + view height of each agent as a target
     float tmesh[kLosPoolCap];
+    float tstop[kLosPoolCap];        // distance to the target capsule: a mesh hit at t <= tstop blocks
     int32_t meta[kLosPoolCap];       // observer | target << 4 | pair << 8
     uint32_t seen[4];                // bit per (observer, opponent slot) pair: 72 bits
     int32_t alive;                   // bit per agent
@@ -175,6 +180,7 @@ struct LosPoolAccess {
     {
         const float4 o = P->origin[P->meta[ray] & 15];
         setRay(r, o.x, o.y, o.z, P->dirs[ray]);
+        r.tStop = P->tstop[ray];
     }
     __device__ __forceinline__ void finish(int ray, bool hit, float t) { P->tmesh[ray] = hit ? t : -1.f; }
 };
@@ -242,10 +248,34 @@ __global__ void __launch_bounds__(kLosWarpsPerCTA * 32, 2) k_los_pool(KernelArgs
                     ok = ok && !(len < kAgentRadius);
                     dir = to_test / len;
                 }
+                // The agent capsules first (utils.cpp:39-61): the sample sees its target only
+                // if, among the capsules, the target is the one traceRayAgainstWorld would
+                // pick -- earlier agents must be strictly farther, later ones not nearer --
+                // and then only if no mesh hit lies at t <= t_target.
+                float t_tgt = 0.f;
+                if (ok) {
+                    const float4 o4 = P.origin[a];
+                    const float a2 = dir.x * dir.x + dir.y * dir.y;
+                    const float dd = a2 + dir.z * dir.z;
+                    {
+                        const float4 t4 = P.target[opp];
+                        t_tgt = rayCapsuleRec(makeCapsuleRec(v3(o4.x, o4.y, o4.z), v3(t4.x, t4.y, t4.z)),
+                                              dir.x, dir.y, dir.z, a2, dd);
+                    }
+                    ok = t_tgt != 0.f;
+                    for (int i = 0; i < kAgents && ok; i++) {
+                        if (i == opp) continue;
+                        const float4 t4 = P.target[i];
+                        const float t = rayCapsuleRec(makeCapsuleRec(v3(o4.x, o4.y, o4.z), v3(t4.x, t4.y, t4.z)),
+                                                      dir.x, dir.y, dir.z, a2, dd);
+                        if (t != 0.f && (i < opp ? !(t_tgt < t) : (t < t_tgt))) ok = false;
+                    }
+                }
                 const unsigned m = __ballot_sync(0xFFFFFFFFu, ok);
                 if (ok) {
                     const int32_t slot = n + __popc(m & lane_lt);
                     P.dirs[slot] = makeRayDirRec(dir);
+                    P.tstop[slot] = t_tgt;
                     P.meta[slot] = a | (opp << 4) | (pair << 8);
                 }
                 n += __popc(m);
@@ -258,23 +288,11 @@ __global__ void __launch_bounds__(kLosWarpsPerCTA * 32, 2) k_los_pool(KernelArgs
             traversePool<kBatch, kRefill>(bvh, acc);
             __syncwarp();
 
-            // ---- phase 3: capsules; the closest hit must be the target
+            // ---- phase 3: visible unless a mesh hit at t <= t_target was accepted
             for (int32_t ray = lane; ray < n; ray += 32) {
-                const int32_t meta = P.meta[ray];
-                const int32_t a = meta & 15, opp = (meta >> 4) & 15, pair = meta >> 8;
-                const RayDirRec &dr = P.dirs[ray];
-                const float4 o4 = P.origin[a];
+                const int32_t pair = P.meta[ray] >> 8;
                 const float tm = P.tmesh[ray];
-                float min_hit_t = tm >= 0.f ? tm : FLT_MAX;
-                int32_t hit_agent = -1;
-#pragma unroll 4
-                for (int i = 0; i < kAgents; i++) {
-                    const float4 t4 = P.target[i];
-                    const CapsuleRec cr = makeCapsuleRec(v3(o4.x, o4.y, o4.z), v3(t4.x, t4.y, t4.z));
-                    const float t = rayCapsuleRec(cr, dr.dx, dr.dy, dr.dz, dr.a2, dr.dd);
-                    if (t != 0 && t < min_hit_t) { min_hit_t = t; hit_agent = i; }
-                }
-                if (hit_agent == opp) atomicOr(&P.seen[pair >> 5], 1u << (pair & 31));
+                if (!(tm >= 0.f && tm <= P.tstop[ray])) atomicOr(&P.seen[pair >> 5], 1u << (pair & 31));
             }
             __syncwarp();
         }
