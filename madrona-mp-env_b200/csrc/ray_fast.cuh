@@ -38,7 +38,8 @@ struct FastChild {
 struct __align__(16) FastNode {
     float minX, minY, minZ, sX;
     float sY, sZ;
-    int32_t pad0, pad1;
+    uint32_t leafMask;      // bit i: child i is a leaf
+    uint32_t triSizes;      // triSize of child i in byte i
     FastChild c[4];
 };
 static_assert(sizeof(FastNode) == 160, "FastNode is 10 x 16 bytes");
@@ -73,7 +74,12 @@ __device__ __forceinline__ FastBVH stageFastBVH(const BVHView &g, void *smem)
             sn[n].sX = u2f((uint32_t)((int32_t)src.expX + 127) << 23);
             sn[n].sY = u2f((uint32_t)((int32_t)src.expY + 127) << 23);
             sn[n].sZ = u2f((uint32_t)((int32_t)src.expZ + 127) << 23);
-            sn[n].pad0 = 0; sn[n].pad1 = 0;
+            uint32_t lm = 0, ts = 0;
+            for (int q = 0; q < 4; q++) {
+                if (src.children[q] != kBVHSentinel && (src.children[q] & 0x80000000)) lm |= 1u << q;
+                ts |= (uint32_t)src.triSize[q] << (8 * q);
+            }
+            sn[n].leafMask = lm; sn[n].triSizes = ts;
         }
     }
     const float *gv = reinterpret_cast<const float *>(g.verts);
@@ -277,22 +283,19 @@ __device__ __forceinline__ void traversePool(const FastBVH &bvh, Pool &pool)
             const int32_t node = stack[--sp];
             const FastNode *nd = bvh.nodes + node;
             const float4 h0 = reinterpret_cast<const float4 *>(nd)[0];    // minX minY minZ sX
-            const float2 h1 = reinterpret_cast<const float2 *>(nd)[2];    // sY sZ
+            const float4 h1 = reinterpret_cast<const float4 *>(nd)[1];    // sY sZ leafMask triSizes
             const float dqx = h0.w * r.invX, dqy = h1.x * r.invY, dqz = h1.y * r.invZ;
             const float oqx = (h0.x - r.ox) * r.invX;
             const float oqy = (h0.y - r.oy) * r.invY;
             const float oqz = (h0.z - r.oz) * r.invZ;
-            tsz = 0;
-            rem = 0;
-            leafmask = 0;
+            leafmask = __float_as_uint(h1.z);
+            tsz = __float_as_uint(h1.w);
+            rem = 0xFu;                  // absent / missed children carry t_near = +inf
 #pragma unroll
             for (int i = 0; i < 4; i++) {
                 const FastChild k = nd->c[i];
                 tn[i] = childNear(k, dqx, dqy, dqz, oqx, oqy, oqz);
                 ch[i] = k.child;
-                tsz |= (uint32_t)k.triSize << (8 * i);
-                rem |= (tn[i] <= t_max ? 1u : 0u) << i;      // t_max only shrinks: a superset
-                leafmask |= (k.child < 0 ? 1u : 0u) << i;
             }
         }
         // Children in order until a leaf needs testing; internal nodes are pushed.
