@@ -66,6 +66,15 @@ typedef struct mpenv_config {
                                     split_i(initKey, episode, GLOBAL world id) (sim.cpp:743-746),
                                     so shards of one big batch reproduce it world for world */
     uint32_t enable_full_team;   /* also fill the FullTeam* tensors every step (sim.cpp:3054-3301) */
+    /* Logs (Config::eventLogPath / recordLogPath / replayLogPath, mgr.hpp:47-49).  NULL = off.
+     * An EMPTY string enables the log in memory only (mpenv_event_log / mpenv_record_log /
+     * mpenv_set_replay_log) without touching the file system.  With any of them on, the step
+     * entry points synchronise with the host every step, as the reference's do
+     * (CUDAImpl::saveEvents, mgr.cpp:417-470). */
+    const char *event_log_dir;   /* directory receiving events.bin + steps.bin (mgr.cpp:218-231) */
+    const char *record_log_path; /* StepLog[num_worlds] appended per step (mgr.cpp:253-257) */
+    const char *replay_log_path; /* StepLog[num_worlds] consumed per step; replaces the gameplay
+                                    systems (pvpReplayLogic, sim.cpp:5587-5604) */
 } mpenv_config;
 
 typedef struct mpenv_handle mpenv_handle;
@@ -179,6 +188,20 @@ int mpenv_episode_stats_async(mpenv_handle *h, void *cuda_stream, int64_t **dev_
 /* Synchronous host variant: reduces on the handle's stream and copies the
  * MPENV_NUM_STATS values to `host_out`. */
 int mpenv_episode_stats(mpenv_handle *h, int64_t *host_out);
+
+/* ---- logs ---------------------------------------------------
+ * Event log: GameEvent (24 B: u32 type, u32 pad, u64 matchID, u32 step, 4 payload
+ * bytes; types.hpp:729-760) and PackedStepSnapshot (192 B, types.hpp:629-634) records of
+ * the LAST step, in host memory owned by the handle (valid until the next step).
+ * Order: world-major; within a world the fire events in agent order (Reload, or
+ * PlayerShot then Kill), then Capture -- the order of the reference's CPU executor
+ * for one world; the reference's order ACROSS worlds is unspecified (atomic append). */
+int mpenv_event_log(mpenv_handle *h, const void **events, uint32_t *num_events,
+                    const void **step_states, uint32_t *num_step_states);
+/* Record log: StepLog[num_worlds] (868 B each, types.hpp:574-589) of the last step. */
+int mpenv_record_log(mpenv_handle *h, const void **step_logs, uint32_t *num_worlds);
+/* Replay from memory (replay_log_path == ""): StepLog[num_worlds] for the NEXT step. */
+int mpenv_set_replay_log(mpenv_handle *h, const void *step_logs, uint64_t bytes);
 
 /* Test / debug surface: full per-world state (see mpenv_state.h). */
 int mpenv_get_world_state(mpenv_handle *h, uint32_t world_idx, mpenv_world_state *out);

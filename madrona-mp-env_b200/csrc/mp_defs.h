@@ -208,7 +208,47 @@ struct WorldState {
     float teamRewards[2];
     int32_t numCrumbs;
     uint32_t nextCrumbUID;
+    uint32_t matchIDValid;                    // Sim::matchID != ~0 (set by the first initWorld after the ctor)
 };
+
+// ---- event log / step snapshots / record + replay log (types.hpp:574-634, 729-760)
+enum EventType : uint32_t { kEvNone = 0, kEvCapture = 1, kEvReload = 2, kEvKill = 4, kEvPlayerShot = 8 };
+struct GameEvent {                                              // types.hpp:729
+    uint32_t type;
+    uint32_t pad0;
+    uint64_t matchID;
+    uint32_t step;
+    uint8_t b0, b1;              // capture: zoneIDX, captureTeam; reload: player, numBulletsAtReloadTime;
+                                 // kill: killer, killed; playerShot: attacker, target
+    uint16_t h1;                 // capture: inZoneMask
+};
+static_assert(sizeof(GameEvent) == 24, "GameEvent is 24 bytes");
+struct PackedPlayerSnapshot {                                   // types.hpp:603
+    int16_t pos[3]; int16_t yaw, pitch;
+    uint8_t magNumBullets, isReloading, hp, flags;
+};
+struct PackedMatchState {                                       // types.hpp:621
+    uint16_t step; uint8_t curZone; int8_t curZoneController;
+    uint16_t zoneStepsRemaining, stepsUntilPoint;
+};
+struct PackedStepSnapshot {                                     // types.hpp:629
+    uint32_t numEvents, eventMask;
+    uint64_t matchID;
+    PackedMatchState matchState;
+    PackedPlayerSnapshot players[kAgents];
+};
+static_assert(sizeof(PackedPlayerSnapshot) == 14, "PackedPlayerSnapshot is 14 bytes");
+static_assert(sizeof(PackedStepSnapshot) == 192, "PackedStepSnapshot is 192 bytes");
+struct AgentLogData {                                           // types.hpp:574
+    Vec3 position; Aim aim; float hp; Magazine mag; StandState standState;
+    int32_t shotAgentIdx; float firedShotT;
+    uint8_t wasKilled, successfullKill, pad[2];
+};
+struct StepLog { AgentLogData agentData[kAgents]; int32_t curStep; };   // types.hpp:586
+static_assert(sizeof(AgentLogData) == 72, "AgentLogData is 72 bytes");
+static_assert(sizeof(StepLog) == 868, "StepLog is 868 bytes");
+constexpr int kEventSlotsPerAgent = 2;      // fireSystem logs Reload, or PlayerShot (+ Kill)
+constexpr int kEventSlotsPerWorld = kAgents * kEventSlotsPerAgent + 1;   // + Capture
 
 struct SpawnUsage {                                             // types.hpp:95
     uint32_t a[kMaxSpawns], b[kMaxSpawns], respawn[kMaxSpawns];
@@ -266,6 +306,9 @@ struct SimConfig {
     uint32_t simFlags;
     int32_t autoReset;
     RandKey initRandKey;                // mgr.cpp:1736-1738
+    int32_t eventLog;                   // TaskConfig::eventGlobalState != nullptr
+    int32_t recordLog;                  // TaskConfig::recordLog != nullptr
+    int32_t replayLog;                  // TaskConfig::replayLog != nullptr
 };
 
 // TrainControl (types.hpp:158), live tensor (mgr.cpp:287-293)
@@ -295,6 +338,12 @@ struct SimPtrs {
     FullTeamGlobalObs *ftGlobal; FullTeamPlayerObs *ftPlayers; FullTeamEnemyObs *ftEnemies;
     FullTeamCommonObs *ftLastKnown; LidarSample *ftFwdLidar; LidarSample *ftRearLidar;
     float *ftReward; int32_t *ftDone;
+    // logs (allocated only when enabled)
+    GameEvent *evAgent;                  // [N][2]: this step's fireSystem events, type 0 = unused
+    GameEvent *evWorld;                  // [W]: this step's Capture event
+    PackedStepSnapshot *stepSnap;        // [W]
+    StepLog *recordLog;                  // [W]
+    StepLog *replayLog;                  // [W]
     // global
     TrainControl *trainCtrl;
 };

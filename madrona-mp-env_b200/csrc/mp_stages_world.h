@@ -11,6 +11,26 @@
 
 namespace mpenv {
 
+// ------------------------------------------------------------- event log
+// logEvent (sim.cpp:23-39).  The reference appends to one global table with an
+// atomic counter, so its order across worlds is whatever the executor produced;
+// here every potential event has a fixed slot ([agent][2] for fireSystem, one
+// Capture per world) and k_event_* compacts the used slots in world-major,
+// agent-major order -- the order the reference's CPU path produces per world.
+MP_HD uint64_t matchIDOf(const Ctx &c, int w)
+{
+    // initWorld (sim.cpp:736-738); ~0 until the first reset after construction (sim.cpp:5971)
+    if (!c.p.world[w].matchIDValid) return ~0ull;
+    return ((uint64_t)(c.cfg.worldIDOffset + (uint32_t)w) << 32) | (uint64_t)c.p.world[w].curEpisodeIdx;
+}
+
+MP_HD GameEvent makeEvent(uint32_t type, uint64_t match_id, int32_t step, uint8_t b0, uint8_t b1, uint16_t h1)
+{
+    GameEvent e;
+    e.type = type; e.pad0 = 0; e.matchID = match_id; e.step = (uint32_t)step; e.b0 = b0; e.b1 = b1; e.h1 = h1;
+    return e;
+}
+
 // ============================================================ stage: fire
 // fireSystem (sim.cpp:1443-1615).  Reads the world's 12 post-move positions
 // and the target's HP / respawn timer; writes only this agent's rows plus
@@ -25,12 +45,23 @@ MP_HD void stageFire(const Ctx &c, int w, int a, const Vec3 *world_pos)
     cs.firedShotT = -FLT_MAX;
     cs.reloadedFullMag = 0;
     const WeaponStats ws = c.mc->weapons[cs.weaponType];
+    const bool log_events = c.cfg.eventLog != 0;
+    GameEvent *ev = nullptr;
+    if (log_events) {
+        ev = p.evAgent + (size_t)idx * kEventSlotsPerAgent;
+        ev[0].type = kEvNone;
+        ev[1].type = kEvNone;
+    }
 
     if (p.alive[idx] == 0.f) { p.combat[idx] = cs; return; }
 
     Magazine mag = p.mag[idx];
     const int32_t fire = p.actDiscrete[idx].fire;
     if (fire == 2) {
+        // sim.cpp:1467-1476 (a reloading agent cannot also shoot this step, so slot 0 is free)
+        if (log_events)
+            ev[0] = makeEvent(kEvReload, matchIDOf(c, w), p.world[w].match.curStep, (uint8_t)a,
+                              (uint8_t)mag.numBullets, 0);
         if (mag.numBullets == ws.magSize) cs.reloadedFullMag = 1;
         mag.numBullets = ws.magSize;
         mag.isReloading = ws.reloadTime;
@@ -77,7 +108,16 @@ MP_HD void stageFire(const Ctx &c, int w, int a, const Vec3 *world_pos)
     if (hit_success) {
         cs.landedShotOn = hit_agent;
         float tgt_hp = p.hp[w * kAgents + hit_agent];
-        if (tgt_hp <= ws.dmgPerBullet) cs.successfulKill = 1;
+        // sim.cpp:1580-1609
+        if (log_events)
+            ev[0] = makeEvent(kEvPlayerShot, matchIDOf(c, w), p.world[w].match.curStep, (uint8_t)a,
+                              (uint8_t)hit_agent, 0);
+        if (tgt_hp <= ws.dmgPerBullet) {
+            cs.successfulKill = 1;
+            if (log_events)
+                ev[1] = makeEvent(kEvKill, matchIDOf(c, w), p.world[w].match.curStep, (uint8_t)a,
+                                  (uint8_t)hit_agent, 0);
+        }
         p.dmg[(size_t)(w * kAgents + hit_agent) * kTeamSize + offsetOf(a)] = ws.dmgPerBullet;
     }
     p.combat[idx] = cs;
@@ -448,7 +488,53 @@ MP_HD void updateFiltersState(const Ctx &c, int w, int32_t cur_step)
     }
 }
 
-// zoneMatchInfoSystem (sim.cpp:4470-4673), Task::Zone, no event log.
+// float -> i16 the way the reference's x86 build does it (cvttss2si to 32 bits,
+// then truncation), not CUDA's saturating cvt.s16.f32.
+MP_HD int16_t f2i16(float v) { return (int16_t)(int32_t)v; }
+
+// writePackedStepSnapshot (sim.cpp:41-126).  eventLoggedInStep is a 0/1 flag
+// there (atomic store of 1), eventMask the OR of the step's event types; both are
+// cleared by every snapshot, and a snapshot is written every step, so they are
+// exactly "this step's" events.
+MP_HD void writePackedStepSnapshot(const Ctx &c, int w, bool captured)
+{
+    const SimPtrs &p = c.p;
+    const int base = w * kAgents;
+    const WorldState &ws = p.world[w];
+    uint32_t mask = captured ? (uint32_t)kEvCapture : 0u;
+    for (int i = 0; i < kAgents * kEventSlotsPerAgent; i++) mask |= p.evAgent[(size_t)base * kEventSlotsPerAgent + i].type;
+    PackedStepSnapshot s;
+    s.numEvents = mask != 0 ? 1u : 0u;
+    s.eventMask = mask;
+    s.matchID = matchIDOf(c, w);
+    s.matchState.step = (uint16_t)ws.match.curStep;
+    s.matchState.curZone = (uint8_t)ws.zone.curZone;
+    s.matchState.curZoneController = (int8_t)(ws.zone.isCaptured ? ws.zone.curControllingTeam : -1);
+    s.matchState.zoneStepsRemaining = (uint16_t)ws.zone.zoneStepsRemaining;
+    s.matchState.stepsUntilPoint = (uint16_t)ws.zone.stepsUntilPoint;
+    for (int i = 0; i < kAgents; i++) {
+        PackedPlayerSnapshot &ps = s.players[i];
+        const int idx = base + i;
+        const Vec3 pos = p.pos[idx];
+        ps.pos[0] = f2i16(pos.x); ps.pos[1] = f2i16(pos.y); ps.pos[2] = f2i16(pos.z);
+        const Aim aim = p.aim[idx];
+        ps.yaw = f2i16(aim.yaw * 32768 / kPi);
+        ps.pitch = f2i16(aim.pitch * 32768 / kPi);
+        const Magazine mag = p.mag[idx];
+        ps.magNumBullets = (uint8_t)mag.numBullets;
+        ps.isReloading = (uint8_t)mag.isReloading;
+        ps.hp = (uint8_t)(int32_t)p.hp[idx];
+        uint8_t flags = 0;
+        if (p.combat[idx].landedShotOn >= 0) flags |= 1u << 1;      // FiredShot
+        const int32_t pose = p.stand[idx].cur;
+        if (pose == 1) flags |= 1u << 2;                             // Crouch
+        else if (pose == 2) flags |= 1u << 3;                        // Prone
+        ps.flags = flags;
+    }
+    p.stepSnap[w] = s;
+}
+
+// zoneMatchInfoSystem (sim.cpp:4470-4673), Task::Zone.
 MP_HD void zoneMatchInfoSystem(const Ctx &c, int w)
 {
     const SimPtrs &p = c.p;
@@ -487,6 +573,30 @@ MP_HD void zoneMatchInfoSystem(const Ctx &c, int w)
         if (zs.isContested) st.contestedSteps += 1;
         if (new_captured) st.numSwaps += 1;
         updateFiltersState(c, w, cur_step);
+        // sim.cpp:4592-4634
+        if (c.cfg.eventLog) {
+            // evWorld[w]: the Capture event (type 0 = none); pad0 = 1 when a step snapshot was written
+            GameEvent cap = makeEvent(kEvNone, 0, 0, 0, 0, 0);
+            if (ws.matchIDValid && new_captured) {
+                Quat to_zone; AABB zbox;
+                zoneFrame(*c.mc, zs.curZone, &to_zone, &zbox);
+                uint32_t in_zone_mask = 0;
+                for (int i = 0; i < kAgents; i++) {
+                    if (teamOf(i) != zs.curControllingTeam) continue;
+                    Vec3 pos = p.pos[base + i];
+                    pos.z += kStandHeight / 2.f;
+                    if (!aabbContains(zbox, rotateVec(to_zone, pos))) continue;
+                    in_zone_mask |= 1u << (uint32_t)i;
+                }
+                cap = makeEvent(kEvCapture, matchIDOf(c, w), mi.curStep, (uint8_t)zs.curZone,
+                                (uint8_t)zs.curControllingTeam, (uint16_t)in_zone_mask);
+            }
+            if (ws.matchIDValid) {
+                cap.pad0 = 1;
+                writePackedStepSnapshot(c, w, new_captured);
+            }
+            p.evWorld[w] = cap;
+        }
     }
     if (match_finished) {
         if (mr.teamObjectivePoints[0] > mr.teamObjectivePoints[1]) mr.winResult = 0;
@@ -780,6 +890,7 @@ MP_HD void initWorld(const Ctx &c, int w, bool triggered_reset)
     }
     // back in initWorld (sim.cpp:829-832)
     for (int t = 0; t < 2; t++) { ws.filtersActive[t] = 0; ws.filtersLastMatchedStep[t] = 0; }
+    ws.matchIDValid = 1;
 }
 
 // resetSystem (sim.cpp:835-872)
@@ -828,6 +939,50 @@ MP_HD void ctorWorld(const Ctx &c, int w)
     p.worldCurriculum[w] = 1;           // WorldCurriculum::FullMatch (sim.cpp:5959)
     initWorld(c, w, true);
     for (int t = 0; t < 2; t++) { ws.filtersActive[t] = 0; ws.filtersLastMatchedStep[t] = -1; }
+    ws.matchIDValid = 0;                // Sim::Sim leaves matchID = ~0 (sim.cpp:5971)
+}
+
+// pvpRecordSystem (sim.cpp:4750-4792), one agent's row; runs after zoneSystem
+// (sim.cpp:5558-5563).
+MP_HD void recordAgent(const Ctx &c, int w, int a)
+{
+    const SimPtrs &p = c.p;
+    const int idx = w * kAgents + a;
+    AgentLogData d;
+    d.position = p.pos[idx];
+    d.aim = p.aim[idx];
+    d.hp = p.hp[idx];
+    d.mag = p.mag[idx];
+    d.standState = p.stand[idx];
+    const CombatState &cs = p.combat[idx];
+    d.shotAgentIdx = cs.landedShotOn;
+    d.firedShotT = cs.firedShotT;
+    d.wasKilled = cs.wasKilled ? 1 : 0;
+    d.successfullKill = cs.successfulKill ? 1 : 0;
+    d.pad[0] = 0; d.pad[1] = 0;
+    p.recordLog[w].agentData[a] = d;
+    if (a == 0) p.recordLog[w].curStep = p.world[w].match.curStep;
+}
+
+// pvpReplaySystem (sim.cpp:4794-4843), one agent's row: the gameplay systems
+// are replaced by the logged state (pvpReplayLogic, sim.cpp:5587-5604).
+MP_HD void replayAgent(const Ctx &c, int w, int a)
+{
+    const SimPtrs &p = c.p;
+    const int idx = w * kAgents + a;
+    const AgentLogData d = p.replayLog[w].agentData[a];
+    p.pos[idx] = d.position;
+    p.aim[idx] = d.aim;
+    p.rot[idx] = quatNormalize(angleAxis(d.aim.yaw, kUp()));
+    p.hp[idx] = d.hp;
+    p.mag[idx] = d.mag;
+    p.stand[idx] = d.standState;
+    CombatState &cs = p.combat[idx];
+    cs.landedShotOn = d.shotAgentIdx;
+    cs.firedShotT = d.firedShotT;
+    cs.wasKilled = d.wasKilled ? 1 : 0;
+    cs.successfulKill = d.successfullKill ? 1 : 0;
+    if (cs.wasKilled) cs.hasDiedDuringEpisode = 1;
 }
 
 // All per-world sequential work of one step after the fire stage, in task
@@ -837,11 +992,19 @@ MP_HD void stageWorld(const Ctx &c, int w)
 {
     const SimPtrs &p = c.p;
     const int base = w * kAgents;
-    for (int i = 0; i < kAgents; i++) applyDmgSystem(p, base + i);
-    if (!(c.cfg.simFlags & kFlagNoRespawn)) spawnAgents(c, w, true);
-    for (int i = 0; i < kAgents; i++) autoHealSystem(p, base + i);
-    zoneSystem(c, w);
-    breadcrumbSystems(c, w);
+    if (c.cfg.replayLog) {
+        p.world[w].match.curStep = p.replayLog[w].curStep;
+        for (int i = 0; i < kAgents; i++) replayAgent(c, w, i);
+        zoneSystem(c, w);
+    } else {
+        for (int i = 0; i < kAgents; i++) applyDmgSystem(p, base + i);
+        if (!(c.cfg.simFlags & kFlagNoRespawn)) spawnAgents(c, w, true);
+        for (int i = 0; i < kAgents; i++) autoHealSystem(p, base + i);
+        zoneSystem(c, w);
+        if (c.cfg.recordLog)
+            for (int i = 0; i < kAgents; i++) recordAgent(c, w, i);
+        breadcrumbSystems(c, w);
+    }
     zoneMatchInfoSystem(c, w);
     evaluateGoalRegionsSystem(c, w);
     for (int i = 0; i < kAgents; i++) exploreVisitedSystem(c, w, base + i);

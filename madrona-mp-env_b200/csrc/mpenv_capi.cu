@@ -64,6 +64,20 @@ struct mpenv_handle {
     int gridMove = 0, gridFire = 0, gridWorld = 0, gridLos = 0, gridObs = 0, gridTeam = 0, gridLidar = 0,
         gridSmall = 0;
     uint32_t stepLaunches = 0, initLaunches = 0;
+    // logs (event log + step snapshots, record log, replay log)
+    bool eventLog = false, recordLog = false, replayLog = false;
+    std::string eventDir, recordPath, replayPath;
+    FILE *evFile = nullptr, *stepsFile = nullptr, *recFile = nullptr, *replayFile = nullptr;
+    uint32_t *devEvOffset = nullptr, *devSnapOffset = nullptr, *devEvTotals = nullptr;
+    GameEvent *devEvOut = nullptr;
+    PackedStepSnapshot *devSnapOut = nullptr;
+    uint32_t *hostEvTotals = nullptr;        // pinned: [0] events, [1] step snapshots
+    GameEvent *hostEvents = nullptr;         // pinned
+    PackedStepSnapshot *hostSnaps = nullptr; // pinned
+    StepLog *hostRecord = nullptr;           // pinned
+    StepLog *hostReplay = nullptr;           // pinned
+    uint32_t lastNumEvents = 0, lastNumSnaps = 0;
+    bool replayPending = false;              // mpenv_set_replay_log() data waiting for the next step
 };
 
 namespace {
@@ -150,11 +164,75 @@ uint32_t launchObsPhase(mpenv_handle *h, cudaStream_t s, bool fork)
 uint32_t launchStep(mpenv_handle *h, cudaStream_t s, bool fork)
 {
     uint32_t n = 0;
-    k_move<<<h->gridMove, 128, h->bvhSmemBytes, s>>>(h->ka); n++;
-    k_fire<<<h->gridFire, 128, h->bvhSmemBytes, s>>>(h->ka); n++;
+    if (!h->replayLog) {
+        k_move<<<h->gridMove, 128, h->bvhSmemBytes, s>>>(h->ka); n++;
+        k_fire<<<h->gridFire, 128, h->bvhSmemBytes, s>>>(h->ka); n++;
+    } else if (h->eventLog) {
+        // pvpReplayLogic has no fireSystem: no fire events this step
+        cudaMemsetAsync(h->ka.ctx.p.evAgent, 0,
+                        (size_t)h->cfg.num_worlds * kAgents * kEventSlotsPerAgent * sizeof(GameEvent), s);
+    }
     k_world<<<h->gridWorld, 128, 0, s>>>(h->ka); n++;
+    if (h->eventLog) {
+        k_event_scan<<<1, 1024, 0, s>>>(h->ka, h->devEvOffset, h->devSnapOffset, h->devEvTotals); n++;
+        k_event_scatter<<<h->gridSmall, 128, 0, s>>>(h->ka, h->devEvOffset, h->devSnapOffset, h->devEvOut,
+                                                      h->devSnapOut); n++;
+    }
     n += launchObsPhase(h, s, fork);
     return n;
+}
+
+// Host side of the logs around one step (CPUImpl::run mgr.cpp:242-271, CUDAImpl::saveEvents
+// mgr.cpp:417-470).  Before: the replay log's next StepLog[W] goes to the device.
+int logsBeforeStep(mpenv_handle *h, cudaStream_t s)
+{
+    if (!h->replayLog) return MPENV_OK;
+    const size_t bytes = (size_t)h->cfg.num_worlds * sizeof(StepLog);
+    if (h->replayFile) {
+        if (fread(h->hostReplay, 1, bytes, h->replayFile) != bytes)
+            return fail(h, MPENV_ERR_IO, "replay log exhausted: " + h->replayPath);
+    } else if (!h->replayPending) {
+        return fail(h, MPENV_ERR_INVALID, "replay from memory: call mpenv_set_replay_log() before every step");
+    }
+    h->replayPending = false;
+    MP_CUDA(h, cudaMemcpyAsync(h->ka.ctx.p.replayLog, h->hostReplay, bytes, cudaMemcpyHostToDevice, s));
+    return MPENV_OK;
+}
+
+// After: counts, then the compacted events / snapshots and the record log come
+// back to pinned host memory and are appended to their files.  Synchronises `s`.
+int logsAfterStep(mpenv_handle *h, cudaStream_t s)
+{
+    if (!h->eventLog && !h->recordLog) {
+        // replay: hostReplay is reused by the next step's read
+        if (h->replayLog) MP_CUDA(h, cudaStreamSynchronize(s));
+        return MPENV_OK;
+    }
+    const size_t W = h->cfg.num_worlds;
+    if (h->eventLog)
+        MP_CUDA(h, cudaMemcpyAsync(h->hostEvTotals, h->devEvTotals, 8, cudaMemcpyDeviceToHost, s));
+    if (h->recordLog)
+        MP_CUDA(h, cudaMemcpyAsync(h->hostRecord, h->ka.ctx.p.recordLog, W * sizeof(StepLog), cudaMemcpyDeviceToHost, s));
+    MP_CUDA(h, cudaStreamSynchronize(s));
+    if (h->eventLog) {
+        h->lastNumEvents = h->hostEvTotals[0];
+        h->lastNumSnaps = h->hostEvTotals[1];
+        if (h->lastNumEvents)
+            MP_CUDA(h, cudaMemcpyAsync(h->hostEvents, h->devEvOut, (size_t)h->lastNumEvents * sizeof(GameEvent),
+                                       cudaMemcpyDeviceToHost, s));
+        if (h->lastNumSnaps)
+            MP_CUDA(h, cudaMemcpyAsync(h->hostSnaps, h->devSnapOut, (size_t)h->lastNumSnaps * sizeof(PackedStepSnapshot),
+                                       cudaMemcpyDeviceToHost, s));
+        MP_CUDA(h, cudaStreamSynchronize(s));
+        // writeGameEvents (mgr.cpp:104-116)
+        if (h->stepsFile && fwrite(h->hostSnaps, sizeof(PackedStepSnapshot), h->lastNumSnaps, h->stepsFile) != h->lastNumSnaps)
+            return fail(h, MPENV_ERR_IO, "short write to " + h->eventDir + "/steps.bin");
+        if (h->evFile && fwrite(h->hostEvents, sizeof(GameEvent), h->lastNumEvents, h->evFile) != h->lastNumEvents)
+            return fail(h, MPENV_ERR_IO, "short write to " + h->eventDir + "/events.bin");
+    }
+    if (h->recFile && fwrite(h->hostRecord, sizeof(StepLog), W, h->recFile) != W)
+        return fail(h, MPENV_ERR_IO, "short write to " + h->recordPath);
+    return MPENV_OK;
 }
 
 uint32_t launchInit(mpenv_handle *h, cudaStream_t s, bool fork)
@@ -245,6 +323,9 @@ void mpenv_destroy(mpenv_handle *h)
     if (h->stepGraph) cudaGraphExecDestroy(h->stepGraph);
     if (h->initGraph) cudaGraphExecDestroy(h->initGraph);
     for (void *p : h->allocs) cudaFree(p);
+    for (FILE *f : { h->evFile, h->stepsFile, h->recFile, h->replayFile }) if (f) fclose(f);
+    for (void *p : { (void *)h->hostEvTotals, (void *)h->hostEvents, (void *)h->hostSnaps, (void *)h->hostRecord,
+                     (void *)h->hostReplay }) if (p) cudaFreeHost(p);
     if (h->copyStream) { cudaStreamSynchronize(h->copyStream); cudaStreamDestroy(h->copyStream); }
     if (h->evSnap) cudaEventDestroy(h->evSnap);
     if (h->evCopied) cudaEventDestroy(h->evCopied);
@@ -280,6 +361,15 @@ int mpenv_create(const mpenv_config *cfg, mpenv_handle **out)
     h->cfg.scene_dir = h->sceneDir.c_str();
     h->device = cfg->gpu_id;
     h->fullTeam = cfg->enable_full_team != 0;
+    h->eventLog = cfg->event_log_dir != nullptr;
+    h->recordLog = cfg->record_log_path != nullptr;
+    h->replayLog = cfg->replay_log_path != nullptr;
+    if (h->eventLog) h->eventDir = cfg->event_log_dir;
+    if (h->recordLog) h->recordPath = cfg->record_log_path;
+    if (h->replayLog) h->replayPath = cfg->replay_log_path;
+    h->cfg.event_log_dir = h->eventLog ? h->eventDir.c_str() : nullptr;
+    h->cfg.record_log_path = h->recordLog ? h->recordPath.c_str() : nullptr;
+    h->cfg.replay_log_path = h->replayLog ? h->replayPath.c_str() : nullptr;
     auto bail = [&](int code) { std::string m = h->error; mpenv_destroy(h); g_create_error = m; return code; };
 
     std::string err;
@@ -331,6 +421,40 @@ int mpenv_create(const mpenv_config *cfg, mpenv_handle **out)
     ka.ctx.cfg.simFlags = cfg->sim_flags;
     ka.ctx.cfg.autoReset = cfg->auto_reset;
     ka.ctx.cfg.initRandKey = randSplit(randInitKey(cfg->rand_seed), 0);     // mgr.cpp:1736-1738
+    ka.ctx.cfg.eventLog = h->eventLog ? 1 : 0;
+    ka.ctx.cfg.recordLog = h->recordLog ? 1 : 0;
+    ka.ctx.cfg.replayLog = h->replayLog ? 1 : 0;
+
+    // logs: files as the reference opens them (mgr.cpp:200-231; FATAL there, an error here)
+    {
+        auto openFile = [&](const std::string &path, const char *mode, FILE **out) -> bool {
+            *out = fopen(path.c_str(), mode);
+            if (!*out) h->error = "failed to open log file " + path;
+            return *out != nullptr;
+        };
+        const size_t W = cfg->num_worlds;
+        if (h->eventLog) {
+            if (!h->eventDir.empty() && (!openFile(h->eventDir + "/events.bin", "wb", &h->evFile) ||
+                                         !openFile(h->eventDir + "/steps.bin", "wb", &h->stepsFile)))
+                return bail(MPENV_ERR_IO);
+            if (!devAlloc((void **)&h->devEvOffset, W * 4) || !devAlloc((void **)&h->devSnapOffset, W * 4) ||
+                !devAlloc((void **)&h->devEvTotals, 8) ||
+                !devAlloc((void **)&h->devEvOut, W * kEventSlotsPerWorld * sizeof(GameEvent)) ||
+                !devAlloc((void **)&h->devSnapOut, W * sizeof(PackedStepSnapshot)))
+                return bail(MPENV_ERR_CUDA);
+            MP_CREATE(cudaMallocHost((void **)&h->hostEvTotals, 8));
+            MP_CREATE(cudaMallocHost((void **)&h->hostEvents, W * kEventSlotsPerWorld * sizeof(GameEvent)));
+            MP_CREATE(cudaMallocHost((void **)&h->hostSnaps, W * sizeof(PackedStepSnapshot)));
+        }
+        if (h->recordLog) {
+            if (!h->recordPath.empty() && !openFile(h->recordPath, "wb", &h->recFile)) return bail(MPENV_ERR_IO);
+            MP_CREATE(cudaMallocHost((void **)&h->hostRecord, W * sizeof(StepLog)));
+        }
+        if (h->replayLog) {
+            if (!h->replayPath.empty() && !openFile(h->replayPath, "rb", &h->replayFile)) return bail(MPENV_ERR_IO);
+            MP_CREATE(cudaMallocHost((void **)&h->hostReplay, W * sizeof(StepLog)));
+        }
+    }
     ka.ctx.mc = h->devConsts;
     ka.ctx.bvh.nodes = h->devNodes;
     ka.ctx.bvh.verts = h->devVerts;
@@ -417,7 +541,42 @@ int mpenv_step_async(mpenv_handle *h, void *cuda_stream)
 {
     if (!h) return MPENV_ERR_INVALID;
     MP_CUDA(h, cudaSetDevice(h->device));
+    int rc = logsBeforeStep(h, (cudaStream_t)cuda_stream);
+    if (rc != MPENV_OK) return rc;
     MP_CUDA(h, cudaGraphLaunch(h->stepGraph, (cudaStream_t)cuda_stream));
+    return logsAfterStep(h, (cudaStream_t)cuda_stream);     // no-op (and no host sync) without logs
+}
+
+int mpenv_event_log(mpenv_handle *h, const void **events, uint32_t *num_events, const void **step_states,
+                    uint32_t *num_step_states)
+{
+    if (!h) return MPENV_ERR_INVALID;
+    if (!h->eventLog) return fail(h, MPENV_ERR_INVALID, "event log not enabled (mpenv_config.event_log_dir)");
+    if (events) *events = h->hostEvents;
+    if (num_events) *num_events = h->lastNumEvents;
+    if (step_states) *step_states = h->hostSnaps;
+    if (num_step_states) *num_step_states = h->lastNumSnaps;
+    return MPENV_OK;
+}
+
+int mpenv_record_log(mpenv_handle *h, const void **step_logs, uint32_t *num_worlds)
+{
+    if (!h) return MPENV_ERR_INVALID;
+    if (!h->recordLog) return fail(h, MPENV_ERR_INVALID, "record log not enabled (mpenv_config.record_log_path)");
+    if (step_logs) *step_logs = h->hostRecord;
+    if (num_worlds) *num_worlds = h->cfg.num_worlds;
+    return MPENV_OK;
+}
+
+int mpenv_set_replay_log(mpenv_handle *h, const void *step_logs, uint64_t bytes)
+{
+    if (!h || !step_logs) return MPENV_ERR_INVALID;
+    if (!h->replayLog || h->replayFile)
+        return fail(h, MPENV_ERR_INVALID, "replay from memory not enabled (mpenv_config.replay_log_path == \"\")");
+    if (bytes != (uint64_t)h->cfg.num_worlds * sizeof(StepLog))
+        return fail(h, MPENV_ERR_INVALID, "mpenv_set_replay_log: size mismatch");
+    memcpy(h->hostReplay, step_logs, bytes);                // every replay step ends with a stream sync
+    h->replayPending = true;
     return MPENV_OK;
 }
 
@@ -675,6 +834,8 @@ int mpenv_get_world_state(mpenv_handle *h, uint32_t world_idx, mpenv_world_state
 int mpenv_step_timed(mpenv_handle *h, float *kernel_ms, const char **kernel_names, uint32_t cap, uint32_t *count)
 {
     if (!h || !kernel_ms || !count) return MPENV_ERR_INVALID;
+    if (h->replayLog || h->eventLog || h->recordLog)
+        return fail(h, MPENV_ERR_INVALID, "mpenv_step_timed: not available with logs enabled");
     MP_CUDA(h, cudaSetDevice(h->device));
     cudaStream_t s = h->stream;
     struct Item { const char *name; };

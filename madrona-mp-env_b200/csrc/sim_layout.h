@@ -78,6 +78,11 @@ inline const BufferDesc *bufferTable(int *count)
         MP_BUF(ftRearLidar, sizeof(LidarSample) * kRearLidarH * kRearLidarW * kTeamSize, kPerTeam),
         MP_BUF(ftReward, 4, kPerTeam),
         MP_BUF(ftDone, 4, kPerTeam),
+        MP_BUF(evAgent, sizeof(GameEvent) * kEventSlotsPerAgent, kPerAgent),
+        MP_BUF(evWorld, sizeof(GameEvent), kPerWorld),
+        MP_BUF(stepSnap, sizeof(PackedStepSnapshot), kPerWorld),
+        MP_BUF(recordLog, sizeof(StepLog), kPerWorld),
+        MP_BUF(replayLog, sizeof(StepLog), kPerWorld),
         MP_BUF(trainCtrl, sizeof(TrainControl), kGlobal),
     };
     *count = (int)(sizeof(table) / sizeof(table[0]));

@@ -122,14 +122,23 @@ __global__ void __launch_bounds__(128) k_world(KernelArgs ka)
         const int base = w * kAgents;
         const bool agent = valid && lane < kAgents;
         const bool lead = valid && lane == 0;
-        if (agent) applyDmgSystem(p, base + lane);
-        __syncwarp();
-        if (lead && !(c.cfg.simFlags & kFlagNoRespawn)) spawnAgents(c, w, true);
-        __syncwarp();
-        if (agent) autoHealSystem(p, base + lane);
-        __syncwarp();
-        zoneSystemCoop(c, w, lane, half, valid);
-        breadcrumbSystemsCoop(c, w, lane, half, valid);
+        if (c.cfg.replayLog) {
+            // pvpReplayLogic (sim.cpp:5587-5604): logged state, then the zone state machine
+            if (lead) p.world[w].match.curStep = p.replayLog[w].curStep;
+            if (agent) replayAgent(c, w, lane);
+            __syncwarp();
+            zoneSystemCoop(c, w, lane, half, valid);
+        } else {
+            if (agent) applyDmgSystem(p, base + lane);
+            __syncwarp();
+            if (lead && !(c.cfg.simFlags & kFlagNoRespawn)) spawnAgents(c, w, true);
+            __syncwarp();
+            if (agent) autoHealSystem(p, base + lane);
+            __syncwarp();
+            zoneSystemCoop(c, w, lane, half, valid);
+            if (c.cfg.recordLog && agent) recordAgent(c, w, lane);
+            breadcrumbSystemsCoop(c, w, lane, half, valid);
+        }
         if (lead) zoneMatchInfoSystem(c, w);
         __syncwarp();
         evaluateGoalRegionsCoop(c, w, lane, half, valid);
@@ -205,6 +214,85 @@ __global__ void __launch_bounds__(160) k_lidar(KernelArgs ka)
         float4 v = make_float4(s.depth, s.isWall, s.isTeammate, s.isOpponent);
         if (ray < 64) reinterpret_cast<float4 *>(c.p.fwdLidar)[(size_t)idx * 64 + ray] = v;
         else reinterpret_cast<float4 *>(c.p.rearLidar)[(size_t)idx * 16 + (ray - 64)] = v;
+    }
+}
+
+// ---- event log compaction (replaces the reference's atomic append, sim.cpp:23-39,
+// with a deterministic order) -------------------------------------------------
+// k_event_scan: ONE CTA; per world counts the used event slots and whether a step
+// snapshot was written, exclusive-scans both over worlds (chunks of 1024 with a
+// carry) and leaves the totals in totals[0..1].
+__global__ void __launch_bounds__(1024) k_event_scan(KernelArgs ka, uint32_t *ev_offset, uint32_t *snap_offset,
+                                                     uint32_t *totals)
+{
+    __shared__ uint32_t warp_sums[2][32];
+    __shared__ uint32_t carry[2];
+    const SimPtrs &p = ka.ctx.p;
+    const int W = (int)ka.ctx.cfg.numWorlds;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (threadIdx.x == 0) { carry[0] = 0; carry[1] = 0; }
+    __syncthreads();
+    for (int w0 = 0; w0 < W; w0 += 1024) {
+        const int w = w0 + threadIdx.x;
+        uint32_t ne = 0, ns = 0;
+        if (w < W) {
+            const GameEvent *ev = p.evAgent + (size_t)w * kAgents * kEventSlotsPerAgent;
+            for (int k = 0; k < kAgents * kEventSlotsPerAgent; k++) ne += ev[k].type != kEvNone ? 1u : 0u;
+            const GameEvent cap = p.evWorld[w];
+            ne += cap.type != kEvNone ? 1u : 0u;
+            ns = cap.pad0 ? 1u : 0u;
+        }
+        uint32_t se = ne, ss = ns;                 // inclusive warp scans
+#pragma unroll
+        for (int off = 1; off < 32; off <<= 1) {
+            const uint32_t te = __shfl_up_sync(0xFFFFFFFFu, se, off), ts = __shfl_up_sync(0xFFFFFFFFu, ss, off);
+            if (lane >= off) { se += te; ss += ts; }
+        }
+        if (lane == 31) { warp_sums[0][warp] = se; warp_sums[1][warp] = ss; }
+        __syncthreads();
+        if (warp == 0) {
+            uint32_t ve = warp_sums[0][lane], vs = warp_sums[1][lane];
+#pragma unroll
+            for (int off = 1; off < 32; off <<= 1) {
+                const uint32_t te = __shfl_up_sync(0xFFFFFFFFu, ve, off), ts = __shfl_up_sync(0xFFFFFFFFu, vs, off);
+                if (lane >= off) { ve += te; vs += ts; }
+            }
+            warp_sums[0][lane] = ve; warp_sums[1][lane] = vs;
+        }
+        __syncthreads();
+        const uint32_t base_e = carry[0] + (warp ? warp_sums[0][warp - 1] : 0u);
+        const uint32_t base_s = carry[1] + (warp ? warp_sums[1][warp - 1] : 0u);
+        if (w < W) { ev_offset[w] = base_e + se - ne; snap_offset[w] = base_s + ss - ns; }
+        __syncthreads();
+        if (threadIdx.x == 0) { carry[0] += warp_sums[0][31]; carry[1] += warp_sums[1][31]; }
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) { totals[0] = carry[0]; totals[1] = carry[1]; }
+}
+
+// k_event_scatter: thread / world copies its used slots (slot order = agent order,
+// Capture last) and its step snapshot to the scanned offsets.
+__global__ void __launch_bounds__(128) k_event_scatter(KernelArgs ka, const uint32_t *ev_offset,
+                                                       const uint32_t *snap_offset, GameEvent *ev_out,
+                                                       PackedStepSnapshot *snap_out)
+{
+    const SimPtrs &p = ka.ctx.p;
+    const int W = (int)ka.ctx.cfg.numWorlds;
+    for (int w = blockIdx.x * blockDim.x + threadIdx.x; w < W; w += gridDim.x * blockDim.x) {
+        uint32_t o = ev_offset[w];
+        const GameEvent *ev = p.evAgent + (size_t)w * kAgents * kEventSlotsPerAgent;
+        for (int k = 0; k < kAgents * kEventSlotsPerAgent; k++) {
+            const GameEvent e = ev[k];
+            if (e.type != kEvNone) ev_out[o++] = e;
+        }
+        GameEvent cap = p.evWorld[w];
+        if (cap.pad0) {
+            const uint4 *src = reinterpret_cast<const uint4 *>(p.stepSnap + w);
+            uint4 *dst = reinterpret_cast<uint4 *>(snap_out + snap_offset[w]);
+#pragma unroll
+            for (int k = 0; k < (int)(sizeof(PackedStepSnapshot) / 16); k++) dst[k] = src[k];
+        }
+        if (cap.type != kEvNone) { cap.pad0 = 0; ev_out[o] = cap; }
     }
 }
 

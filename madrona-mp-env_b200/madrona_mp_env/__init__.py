@@ -51,7 +51,9 @@ class _Config(C.Structure):
                 ("auto_reset", C.c_int32), ("sim_flags", C.c_uint32), ("task_type", C.c_uint32),
                 ("team_size", C.c_uint32), ("num_pbt_policies", C.c_uint32),
                 ("policy_history_size", C.c_uint32), ("scene_dir", C.c_char_p),
-                ("world_id_offset", C.c_uint32), ("enable_full_team", C.c_uint32)]
+                ("world_id_offset", C.c_uint32), ("enable_full_team", C.c_uint32),
+                ("event_log_dir", C.c_char_p), ("record_log_path", C.c_char_p),
+                ("replay_log_path", C.c_char_p)]
 
 
 class _TensorDesc(C.Structure):
@@ -136,17 +138,18 @@ class SimManager:
                  curriculum_data_path=None, world_id_offset=0, enable_full_team=True):
         if int(exec_mode) != int(ExecMode.CUDA):
             raise ValueError("madrona_mp_env (B200): only ExecMode.CUDA exists; there is no CPU path")
-        for name, v in (("replay_log_path", replay_log_path), ("record_log_path", record_log_path),
-                        ("event_log_path", event_log_path), ("curriculum_data_path", curriculum_data_path)):
-            if v is not None:
-                raise NotImplementedError(f"{name}: record/replay/event logs are outside this build's scope")
+        if curriculum_data_path is not None:
+            raise NotImplementedError("curriculum_data_path: the trajectory curriculum is outside this build's scope")
         if train_flank:
             raise NotImplementedError("train_flank (RewardMode::Flank) is outside this build's scope")
         self._lib = _load()
         self._scene = os.fsencode(scene_path)
+        # mgr.hpp:47-49; the C ABI copies the strings
+        enc = lambda v: None if v is None else os.fsencode(v)
         cfg = _Config(int(gpu_id), int(num_worlds), int(rand_seed), int(bool(auto_reset)),
                       int(sim_flags), int(task_type), int(team_size), int(num_pbt_policies),
-                      int(policy_history_size), self._scene, int(world_id_offset), int(enable_full_team))
+                      int(policy_history_size), self._scene, int(world_id_offset), int(enable_full_team),
+                      enc(event_log_path), enc(record_log_path), enc(replay_log_path))
         self._h = C.c_void_p()
         rc = self._lib.mpenv_create(C.byref(cfg), C.byref(self._h))
         if rc != 0:

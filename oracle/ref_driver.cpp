@@ -59,6 +59,9 @@ struct RefConfig {
     uint32_t policyHistorySize;
     uint32_t worldIDOffset;   // global id of world 0 (multi-GPU shards)
     uint32_t numThreads;
+    uint32_t enableEventLog;  // TaskConfig::eventGlobalState (mgr.cpp:1227, 1777)
+    uint32_t enableRecordLog; // TaskConfig::recordLog (mgr.cpp:1774)
+    uint32_t enableReplayLog; // TaskConfig::replayLog (mgr.cpp:1775)
 };
 
 struct RefSim {
@@ -79,6 +82,8 @@ struct RefSim {
     WeaponStats weapon;
     TrainControl trainCtrl;
     SpawnCurriculum spawnCurriculum;
+    EventLogGlobalState eventGlobal { 0, 0 };
+    std::vector<StepLog> recordLog, replayLog;
     std::string error;
 };
 
@@ -326,9 +331,11 @@ void * ref_create(const RefConfig *cfg, const char *scene_dir,
     tc.rewardMode = RewardMode::Default;
     tc.highlevelMove = false;
     tc.viz = nullptr;
-    tc.recordLog = nullptr;
-    tc.replayLog = nullptr;
-    tc.eventGlobalState = nullptr;
+    if (cfg->enableRecordLog) s->recordLog.resize(cfg->numWorlds);
+    if (cfg->enableReplayLog) s->replayLog.resize(cfg->numWorlds);
+    tc.recordLog = cfg->enableRecordLog ? s->recordLog.data() : nullptr;
+    tc.replayLog = cfg->enableReplayLog ? s->replayLog.data() : nullptr;
+    tc.eventGlobalState = cfg->enableEventLog ? &s->eventGlobal : nullptr;
     tc.goalRegions = s->goalRegions.data();
     tc.numGoalRegions = (int32_t)s->goalRegions.size();
     tc.numEpisodes = 0;
@@ -389,6 +396,53 @@ void ref_step(void *h)
 }
 
 uint32_t ref_num_threads(void *h) { return ((RefSim *)h)->cfg.numThreads; }
+
+// The step's GameEvent / PackedStepSnapshot rows (the temporaries cleared at the
+// start of every Step graph, sim.cpp:5344-5345), gathered world by world in
+// table order -- what CPUImpl::run hands to writeGameEvents (mgr.cpp:259-268)
+// for a single-threaded executor.  which: 0 = events, 1 = step snapshots.
+// Returns the number of rows, or -1 if `cap_rows` is too small.
+int64_t ref_read_event_log(void *h, uint32_t which, void *dst, uint64_t cap_rows)
+{
+    RefSim *s = (RefSim *)h;
+    const uint32_t arch = which == 0 ? shim::TypeID<GameEventEntity>::get()
+                                     : shim::TypeID<PackedStepSnapshotEntity>::get();
+    const uint32_t comp = which == 0 ? shim::TypeID<GameEvent>::get()
+                                     : shim::TypeID<PackedStepSnapshot>::get();
+    const uint64_t row_bytes = which == 0 ? sizeof(GameEvent) : sizeof(PackedStepSnapshot);
+    uint64_t n = 0;
+    for (auto &w : s->worlds) {
+        shim::Table &t = w.tables[arch];
+        int col = w.colIndex(arch, comp);
+        if (n + (uint64_t)t.numRows > cap_rows) return -1;
+        memcpy((char *)dst + n * row_bytes, t.cols[col], (uint64_t)t.numRows * row_bytes);
+        n += (uint64_t)t.numRows;
+    }
+    return (int64_t)n;
+}
+
+// The global counters logEvent / writePackedStepSnapshot bump (sim.cpp:31-32, 58-59);
+// reset to zero as CPUImpl::run does after writing (mgr.cpp:267-268).
+void ref_event_log_counts(void *h, uint32_t *num_events, uint32_t *num_step_states)
+{
+    RefSim *s = (RefSim *)h;
+    *num_events = s->eventGlobal.numEvents;
+    *num_step_states = s->eventGlobal.numStepStates;
+    s->eventGlobal.numEvents = 0;
+    s->eventGlobal.numStepStates = 0;
+}
+
+uint32_t ref_event_row_bytes(uint32_t which)
+{
+    return which == 0 ? (uint32_t)sizeof(GameEvent) : (uint32_t)sizeof(PackedStepSnapshot);
+}
+
+// StepLog buffers (numWorlds x sizeof(StepLog)): the record log is filled by
+// pvpRecordSystem every step; the replay log must be filled by the caller
+// before each step (CPUImpl::run, mgr.cpp:244-257).
+void * ref_record_log(void *h) { RefSim *s = (RefSim *)h; return s->recordLog.empty() ? nullptr : s->recordLog.data(); }
+void * ref_replay_log(void *h) { RefSim *s = (RefSim *)h; return s->replayLog.empty() ? nullptr : s->replayLog.data(); }
+uint32_t ref_step_log_bytes() { return (uint32_t)sizeof(StepLog); }
 
 // Bytes per row of exported slot `export_id` (ExportID, sim.hpp:15-66) and
 // the number of rows per world; 0 if the slot is not exported.

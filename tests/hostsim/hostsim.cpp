@@ -61,6 +61,7 @@ struct HostSimConfig {
     uint32_t numWorlds, randSeed;
     int32_t autoReset;
     uint32_t simFlags, worldIDOffset, enableFullTeam;
+    uint32_t enableEventLog, enableRecordLog, enableReplayLog;
 };
 
 void *hostsim_create(const HostSimConfig *cfg, const char *scene_dir)
@@ -81,6 +82,9 @@ void *hostsim_create(const HostSimConfig *cfg, const char *scene_dir)
     c.cfg.simFlags = cfg->simFlags;
     c.cfg.autoReset = cfg->autoReset;
     c.cfg.initRandKey = randSplit(randInitKey(cfg->randSeed), 0);    // mgr.cpp:1736-1738
+    c.cfg.eventLog = cfg->enableEventLog ? 1 : 0;
+    c.cfg.recordLog = cfg->enableRecordLog ? 1 : 0;
+    c.cfg.replayLog = cfg->enableReplayLog ? 1 : 0;
     c.mc = &s->consts;
     c.bvh.nodes = s->assets.nodes.data();
     c.bvh.verts = s->assets.verts.data();
@@ -123,12 +127,45 @@ void hostsim_step(void *h)
     HostSim *s = (HostSim *)h;
     const Ctx &c = s->ctx;
     const int W = (int)s->numWorlds;
-    for (int i = 0; i < W * kAgents; i++) stageMove(c, i);
-    for (int w = 0; w < W; w++)
-        for (int a = 0; a < kAgents; a++) stageFire(c, w, a, c.p.pos + (size_t)w * kAgents);
+    if (!c.cfg.replayLog) {
+        for (int i = 0; i < W * kAgents; i++) stageMove(c, i);
+        for (int w = 0; w < W; w++)
+            for (int a = 0; a < kAgents; a++) stageFire(c, w, a, c.p.pos + (size_t)w * kAgents);
+    } else if (c.cfg.eventLog) {
+        // no fireSystem in the replay graph: no fire events this step
+        for (size_t i = 0; i < (size_t)W * kAgents * kEventSlotsPerAgent; i++) c.p.evAgent[i].type = kEvNone;
+    }
     for (int w = 0; w < W; w++) stageWorld(c, w);
     obsPhase(*s);
 }
+
+// The step's events / step snapshots compacted in world-major, agent-major slot
+// order (what k_event_scan / k_event_scatter produce on the device).
+int64_t hostsim_read_event_log(void *h, uint32_t which, void *dst, uint64_t cap_rows)
+{
+    HostSim *s = (HostSim *)h;
+    const SimPtrs &p = s->ctx.p;
+    uint64_t n = 0;
+    for (uint32_t w = 0; w < s->numWorlds; w++) {
+        if (which == 0) {
+            for (int k = 0; k < kEventSlotsPerWorld; k++) {
+                GameEvent e = k < kAgents * kEventSlotsPerAgent
+                    ? p.evAgent[(size_t)w * kAgents * kEventSlotsPerAgent + k] : p.evWorld[w];
+                if (e.type == kEvNone) continue;
+                if (n >= cap_rows) return -1;
+                e.pad0 = 0;
+                ((GameEvent *)dst)[n++] = e;
+            }
+        } else if (p.evWorld[w].pad0) {
+            if (n >= cap_rows) return -1;
+            ((PackedStepSnapshot *)dst)[n++] = p.stepSnap[w];
+        }
+    }
+    return (int64_t)n;
+}
+
+void *hostsim_record_log(void *h) { return ((HostSim *)h)->ctx.p.recordLog; }
+void *hostsim_replay_log(void *h) { return ((HostSim *)h)->ctx.p.replayLog; }
 
 int hostsim_export_bytes(void *h, uint32_t id, uint64_t *bytes)
 {

@@ -258,11 +258,55 @@ class RefConfig(C.Structure):
     _fields_ = [("numWorlds", C.c_uint32), ("randSeed", C.c_uint32), ("autoReset", C.c_int32),
                 ("simFlags", C.c_uint32), ("taskType", C.c_uint32), ("teamSize", C.c_uint32),
                 ("numPBTPolicies", C.c_uint32), ("policyHistorySize", C.c_uint32),
-                ("worldIDOffset", C.c_uint32), ("numThreads", C.c_uint32)]
+                ("worldIDOffset", C.c_uint32), ("numThreads", C.c_uint32),
+                ("enableEventLog", C.c_uint32), ("enableRecordLog", C.c_uint32),
+                ("enableReplayLog", C.c_uint32)]
+
+
+# Log record layouts (reference types.hpp:574-634, 729-760; csrc/mp_defs.h).
+EVENT_DT = np.dtype([("type", "<u4"), ("pad0", "<u4"), ("matchID", "<u8"), ("step", "<u4"),
+                     ("b0", "u1"), ("b1", "u1"), ("h1", "<u2")])
+PLAYER_SNAP_DT = np.dtype([("pos", "<i2", (3,)), ("yaw", "<i2"), ("pitch", "<i2"), ("magNumBullets", "u1"),
+                           ("isReloading", "u1"), ("hp", "u1"), ("flags", "u1")])
+SNAP_DT = np.dtype([("numEvents", "<u4"), ("eventMask", "<u4"), ("matchID", "<u8"), ("step", "<u2"),
+                    ("curZone", "u1"), ("curZoneController", "i1"), ("zoneStepsRemaining", "<u2"),
+                    ("stepsUntilPoint", "<u2"), ("players", PLAYER_SNAP_DT, (12,))])
+AGENT_LOG_DT = np.dtype([("position", "<f4", (3,)), ("aim", "<f4", (6,)), ("hp", "<f4"), ("mag", "<i4", (2,)),
+                         ("standState", "<i4", (3,)), ("shotAgentIdx", "<i4"), ("firedShotT", "<f4"),
+                         ("wasKilled", "u1"), ("successfullKill", "u1"), ("pad", "u1", (2,))])
+STEP_LOG_DT = np.dtype([("agentData", AGENT_LOG_DT, (12,)), ("curStep", "<i4")])
+assert EVENT_DT.itemsize == 24 and SNAP_DT.itemsize == 192 and STEP_LOG_DT.itemsize == 868
+EV_CAPTURE, EV_RELOAD, EV_KILL, EV_PLAYER_SHOT = 1, 2, 4, 8
+
+
+def canonical_events(ev):
+    """Events with the bytes the reference leaves unspecified masked out: struct
+    padding, and the upper half of the 4-byte payload union for the 2-byte
+    payloads (Reload / Kill / PlayerShot)."""
+    ev = ev.copy()
+    ev["pad0"] = 0
+    ev["h1"][ev["type"] != EV_CAPTURE] = 0
+    return ev
+
+
+def canonical_step_logs(sl):
+    sl = sl.copy()
+    sl["agentData"]["pad"] = 0
+    return sl
 
 
 class _SimBase:
     num_worlds = 0
+
+    def event_log(self):
+        """(events, step_snapshots) of the last step as structured arrays."""
+        raise NotImplementedError
+
+    def record_log(self):
+        raise NotImplementedError
+
+    def set_replay_log(self, step_logs):
+        raise NotImplementedError
 
     def export(self, name):
         kind, cols, dt = EXPORT_SHAPES[name]
@@ -292,7 +336,8 @@ class Oracle(_SimBase):
     oracle/shim.  det=True routes sinf/cosf/logf/atan2f/asinf to mp_math.h."""
 
     def __init__(self, num_worlds, rand_seed=10, auto_reset=False, sim_flags=0, det=True,
-                 world_id_offset=0, num_threads=1, scene=SCENE, bvh=None):
+                 world_id_offset=0, num_threads=1, scene=SCENE, bvh=None, event_log=False,
+                 record_log=False, replay_log=False):
         build_oracle()
         self.lib = C.CDLL(REF_DET_SO if det else REF_SO)
         L = self.lib
@@ -319,7 +364,16 @@ class Oracle(_SimBase):
         v20 = np.zeros((verts.shape[0], 5), dtype=np.float32)     # BVHVertex {pos, uv}
         v20[:, :3] = verts
         cfg = RefConfig(num_worlds, rand_seed, int(auto_reset), sim_flags, 2, 6, 0, 1,
-                        world_id_offset, num_threads)
+                        world_id_offset, num_threads, int(event_log), int(record_log), int(replay_log))
+        L.ref_read_event_log.restype = C.c_int64
+        L.ref_read_event_log.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint64]
+        L.ref_event_log_counts.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+        L.ref_record_log.restype = C.c_void_p
+        L.ref_record_log.argtypes = [C.c_void_p]
+        L.ref_replay_log.restype = C.c_void_p
+        L.ref_replay_log.argtypes = [C.c_void_p]
+        assert L.ref_event_row_bytes(0) == EVENT_DT.itemsize and L.ref_event_row_bytes(1) == SNAP_DT.itemsize
+        assert L.ref_step_log_bytes() == STEP_LOG_DT.itemsize
         root = np.array(list(info.root_aabb), dtype=np.float32)
         self.h = L.ref_create(C.byref(cfg), scene.encode(), nodes.ctypes.data, info.num_nodes,
                               v20.ctypes.data, verts.shape[0], info.num_leaves, root.ctypes.data)
@@ -340,6 +394,28 @@ class Oracle(_SimBase):
 
     def num_threads(self):
         return self.lib.ref_num_threads(self.h)
+
+    def event_log(self):
+        ev = np.zeros(self.num_worlds * 32, EVENT_DT)
+        sn = np.zeros(self.num_worlds, SNAP_DT)
+        ne = self.lib.ref_read_event_log(self.h, 0, ev.ctypes.data, len(ev))
+        ns = self.lib.ref_read_event_log(self.h, 1, sn.ctypes.data, len(sn))
+        assert ne >= 0 and ns >= 0
+        cnt = np.zeros(2, np.uint32)
+        self.lib.ref_event_log_counts(self.h, cnt[0:].ctypes.data, cnt[1:].ctypes.data)
+        assert (int(cnt[0]), int(cnt[1])) == (ne, ns), "EventLogGlobalState counters disagree with the tables"
+        return ev[:ne], sn[:ns]
+
+    def record_log(self):
+        ptr = self.lib.ref_record_log(self.h)
+        assert ptr
+        buf = (C.c_char * (self.num_worlds * STEP_LOG_DT.itemsize)).from_address(ptr)
+        return np.frombuffer(buf, STEP_LOG_DT).copy()
+
+    def set_replay_log(self, step_logs):
+        ptr = self.lib.ref_replay_log(self.h)
+        assert ptr and step_logs.nbytes == self.num_worlds * STEP_LOG_DT.itemsize
+        C.memmove(ptr, np.ascontiguousarray(step_logs).ctypes.data, step_logs.nbytes)
 
     def _read(self, eid, arr):
         rc = self.lib.ref_read_export(self.h, eid, arr.ctypes.data, arr.nbytes)
@@ -382,14 +458,16 @@ class Oracle(_SimBase):
 # ------------------------------------------------------------------ hostsim
 class HostSimConfig(C.Structure):
     _fields_ = [("numWorlds", C.c_uint32), ("randSeed", C.c_uint32), ("autoReset", C.c_int32),
-                ("simFlags", C.c_uint32), ("worldIDOffset", C.c_uint32), ("enableFullTeam", C.c_uint32)]
+                ("simFlags", C.c_uint32), ("worldIDOffset", C.c_uint32), ("enableFullTeam", C.c_uint32),
+                ("enableEventLog", C.c_uint32), ("enableRecordLog", C.c_uint32),
+                ("enableReplayLog", C.c_uint32)]
 
 
 class HostSim(_SimBase):
     """Device stage functions compiled for the host (tests only)."""
 
     def __init__(self, num_worlds, rand_seed=10, auto_reset=False, sim_flags=0, world_id_offset=0,
-                 full_team=True, scene=SCENE):
+                 full_team=True, scene=SCENE, event_log=False, record_log=False, replay_log=False):
         self.lib = C.CDLL(build_hostsim())
         L = self.lib
         L.hostsim_create.restype = C.c_void_p
@@ -403,7 +481,13 @@ class HostSim(_SimBase):
         L.hostsim_sphere_cast.restype = C.c_float
         L.hostsim_sphere_cast.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_float, C.c_void_p]
         cfg = HostSimConfig(num_worlds, rand_seed, int(auto_reset), sim_flags, world_id_offset,
-                            int(full_team))
+                            int(full_team), int(event_log), int(record_log), int(replay_log))
+        L.hostsim_read_event_log.restype = C.c_int64
+        L.hostsim_read_event_log.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint64]
+        L.hostsim_record_log.restype = C.c_void_p
+        L.hostsim_record_log.argtypes = [C.c_void_p]
+        L.hostsim_replay_log.restype = C.c_void_p
+        L.hostsim_replay_log.argtypes = [C.c_void_p]
         self.h = L.hostsim_create(C.byref(cfg), scene.encode())
         if not self.h:
             raise RuntimeError("hostsim_create failed")
@@ -419,6 +503,24 @@ class HostSim(_SimBase):
 
     def step(self):
         self.lib.hostsim_step(self.h)
+
+    def event_log(self):
+        ev = np.zeros(self.num_worlds * 32, EVENT_DT)
+        sn = np.zeros(self.num_worlds, SNAP_DT)
+        ne = self.lib.hostsim_read_event_log(self.h, 0, ev.ctypes.data, len(ev))
+        ns = self.lib.hostsim_read_event_log(self.h, 1, sn.ctypes.data, len(sn))
+        assert ne >= 0 and ns >= 0
+        return ev[:ne], sn[:ns]
+
+    def record_log(self):
+        ptr = self.lib.hostsim_record_log(self.h)
+        buf = (C.c_char * (self.num_worlds * STEP_LOG_DT.itemsize)).from_address(ptr)
+        return np.frombuffer(buf, STEP_LOG_DT).copy()
+
+    def set_replay_log(self, step_logs):
+        ptr = self.lib.hostsim_replay_log(self.h)
+        assert step_logs.nbytes == self.num_worlds * STEP_LOG_DT.itemsize
+        C.memmove(ptr, np.ascontiguousarray(step_logs).ctypes.data, step_logs.nbytes)
 
     def _read(self, eid, arr):
         rc = self.lib.hostsim_read_export(self.h, eid, arr.ctypes.data, arr.nbytes)
@@ -540,7 +642,9 @@ class MpenvConfig(C.Structure):
                 ("auto_reset", C.c_int32), ("sim_flags", C.c_uint32), ("task_type", C.c_uint32),
                 ("team_size", C.c_uint32), ("num_pbt_policies", C.c_uint32),
                 ("policy_history_size", C.c_uint32), ("scene_dir", C.c_char_p),
-                ("world_id_offset", C.c_uint32), ("enable_full_team", C.c_uint32)]
+                ("world_id_offset", C.c_uint32), ("enable_full_team", C.c_uint32),
+                ("event_log_dir", C.c_char_p), ("record_log_path", C.c_char_p),
+                ("replay_log_path", C.c_char_p)]
 
 
 class TensorDesc(C.Structure):
@@ -569,6 +673,10 @@ def load_product():
     L.mpenv_host_alloc.argtypes = [C.c_uint64, C.POINTER(C.c_void_p)]
     L.mpenv_host_free.argtypes = [C.c_void_p]
     L.mpenv_trigger_reset.argtypes = [C.c_void_p, C.c_int32]
+    L.mpenv_event_log.argtypes = [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_uint32),
+                                  C.POINTER(C.c_void_p), C.POINTER(C.c_uint32)]
+    L.mpenv_record_log.argtypes = [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_uint32)]
+    L.mpenv_set_replay_log.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64]
     return L
 
 
@@ -576,11 +684,15 @@ class GpuSim(_SimBase):
     """The product: libmpenv_b200.so through its C ABI, host buffers in and out."""
 
     def __init__(self, num_worlds, rand_seed=10, auto_reset=False, sim_flags=0, world_id_offset=0,
-                 full_team=True, scene=SCENE, gpu_id=0):
+                 full_team=True, scene=SCENE, gpu_id=0, event_log=False, record_log=False, replay_log=False):
+        """event_log / record_log / replay_log: False = off, True = in memory only,
+        a path = the reference's files (event_log: directory)."""
         self.lib = load_product()
         self._scene = scene.encode()
+        path = lambda v: None if v is False or v is None else (b"" if v is True else str(v).encode())
+        self._log_paths = [path(event_log), path(record_log), path(replay_log)]
         cfg = MpenvConfig(gpu_id, num_worlds, rand_seed, int(auto_reset), sim_flags, 2, 6, 0, 1,
-                          self._scene, world_id_offset, int(full_team))
+                          self._scene, world_id_offset, int(full_team), *self._log_paths)
         self.h = C.c_void_p()
         rc = self.lib.mpenv_create(C.byref(cfg), C.byref(self.h))
         if rc != 0:
@@ -612,6 +724,26 @@ class GpuSim(_SimBase):
 
     def _state(self, w, ws):
         self._check(self.lib.mpenv_get_world_state(self.h, w, C.byref(ws)), "get_world_state")
+
+    def event_log(self):
+        ev, sn = C.c_void_p(), C.c_void_p()
+        ne, ns = C.c_uint32(), C.c_uint32()
+        self._check(self.lib.mpenv_event_log(self.h, C.byref(ev), C.byref(ne), C.byref(sn), C.byref(ns)), "event_log")
+        def view(ptr, n, dt):
+            if n == 0:
+                return np.zeros(0, dt)
+            return np.frombuffer((C.c_char * (n * dt.itemsize)).from_address(ptr.value), dt).copy()
+        return view(ev, ne.value, EVENT_DT), view(sn, ns.value, SNAP_DT)
+
+    def record_log(self):
+        ptr, n = C.c_void_p(), C.c_uint32()
+        self._check(self.lib.mpenv_record_log(self.h, C.byref(ptr), C.byref(n)), "record_log")
+        buf = (C.c_char * (n.value * STEP_LOG_DT.itemsize)).from_address(ptr.value)
+        return np.frombuffer(buf, STEP_LOG_DT).copy()
+
+    def set_replay_log(self, step_logs):
+        a = np.ascontiguousarray(step_logs)
+        self._check(self.lib.mpenv_set_replay_log(self.h, a.ctypes.data, a.nbytes), "set_replay_log")
 
     def launches(self):
         a, b = C.c_uint32(), C.c_uint32()
