@@ -75,6 +75,11 @@ typedef struct mpenv_config {
     const char *record_log_path; /* StepLog[num_worlds] appended per step (mgr.cpp:253-257) */
     const char *replay_log_path; /* StepLog[num_worlds] consumed per step; replaces the gameplay
                                     systems (pvpReplayLogic, sim.cpp:5587-5604) */
+    /* Config::curriculumDataPath (mgr.hpp:50, mgr.cpp:1424-1441): a file of CurriculumSnapshot
+     * records (176 B = PackedMatchState + 12 PackedPlayerSnapshot, types.hpp:816-819; the body
+     * of a steps.bin record after its 16-byte header).  Half of the non-eval episodes then
+     * start from a random snapshot (level_gen.cpp:498-581).  NULL = off. */
+    const char *curriculum_data_path;
 } mpenv_config;
 
 typedef struct mpenv_handle mpenv_handle;

@@ -247,6 +247,11 @@ struct AgentLogData {                                           // types.hpp:574
 struct StepLog { AgentLogData agentData[kAgents]; int32_t curStep; };   // types.hpp:586
 static_assert(sizeof(AgentLogData) == 72, "AgentLogData is 72 bytes");
 static_assert(sizeof(StepLog) == 868, "StepLog is 868 bytes");
+struct CurriculumSnapshot {                                     // types.hpp:816
+    PackedMatchState matchState;
+    PackedPlayerSnapshot players[kAgents];
+};
+static_assert(sizeof(CurriculumSnapshot) == 176, "CurriculumSnapshot is 176 bytes");
 constexpr int kEventSlotsPerAgent = 2;      // fireSystem logs Reload, or PlayerShot (+ Kill)
 constexpr int kEventSlotsPerWorld = kAgents * kEventSlotsPerAgent + 1;   // + Capture
 
@@ -309,6 +314,7 @@ struct SimConfig {
     int32_t eventLog;                   // TaskConfig::eventGlobalState != nullptr
     int32_t recordLog;                  // TaskConfig::recordLog != nullptr
     int32_t replayLog;                  // TaskConfig::replayLog != nullptr
+    int32_t numCurriculumSnapshots;     // TrajectoryCurriculum::numSnapshots (mgr.cpp:1419-1441)
 };
 
 // TrainControl (types.hpp:158), live tensor (mgr.cpp:287-293)
@@ -345,6 +351,7 @@ struct SimPtrs {
     StepLog *recordLog;                  // [W]
     StepLog *replayLog;                  // [W]
     // global
+    const CurriculumSnapshot *curriculum;   // TrajectoryCurriculum::snapshots (not in the buffer table)
     TrainControl *trainCtrl;
 };
 

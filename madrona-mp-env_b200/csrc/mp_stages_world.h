@@ -888,6 +888,37 @@ MP_HD void initWorld(const Ctx &c, int w, bool triggered_reset)
         for (int k = 0; k < 24; k++) z[k] = 0.f;
         for (int j = 0; j < kTeamSize; j++) p.ftLastKnown[((size_t)w * 2 + t) * kTeamSize + j] = zero;
     }
+    // Trajectory curriculum (level_gen.cpp:498-581): half of the episodes (not in
+    // eval mode) start from a recorded mid-match snapshot instead of the spawn state.
+    if (c.cfg.numCurriculumSnapshots > 0 && rngUniform(base_rng) < 0.5f && !tc.evalMode) {
+        const int32_t snapshot_idx = rngI32(base_rng, 0, c.cfg.numCurriculumSnapshots);
+        const CurriculumSnapshot snap = p.curriculum[snapshot_idx];
+        zs.curZone = snap.matchState.curZone;
+        if (snap.matchState.curZoneController == -1) {
+            zs.curControllingTeam = -1;
+            zs.isCaptured = 0;
+        } else {
+            zs.isCaptured = 1;
+            zs.curControllingTeam = snap.matchState.curZoneController;
+            zs.stepsUntilPoint = snap.matchState.stepsUntilPoint;
+            zs.zoneStepsRemaining = snap.matchState.zoneStepsRemaining;
+        }
+        mi.curStep = snap.matchState.step;
+        for (int i = 0; i < kAgents; i++) {
+            const int a = mi.teamA == 0 ? i : (i < kAgents / 2 ? kAgents / 2 + i : i - kAgents / 2);
+            const int idx = base + a;
+            const PackedPlayerSnapshot ps = snap.players[i];
+            p.pos[idx] = v3((float)ps.pos[0], (float)ps.pos[1], (float)ps.pos[2]);
+            const Aim aim = computeAim((float)ps.yaw * kPi / 32768.f, (float)ps.pitch * kPi / 32768.f);
+            p.aim[idx] = aim;
+            p.rot[idx] = quatNormalize(angleAxis(aim.yaw, kUp()));
+            p.hp[idx] = (float)ps.hp;
+            Magazine mag; mag.numBullets = ps.magNumBullets; mag.isReloading = ps.isReloading;
+            p.mag[idx] = mag;
+            if (ps.flags & (1u << 2)) { StandState st; st.cur = 1; st.tgt = 1; st.transition = 0; p.stand[idx] = st; }
+            if (ps.flags & (1u << 3)) { StandState st; st.cur = 2; st.tgt = 2; st.transition = 0; p.stand[idx] = st; }
+        }
+    }
     // back in initWorld (sim.cpp:829-832)
     for (int t = 0; t < 2; t++) { ws.filtersActive[t] = 0; ws.filtersLastMatchedStep[t] = 0; }
     ws.matchIDValid = 1;

@@ -76,6 +76,7 @@ struct mpenv_handle {
     PackedStepSnapshot *hostSnaps = nullptr; // pinned
     StepLog *hostRecord = nullptr;           // pinned
     StepLog *hostReplay = nullptr;           // pinned
+    std::string curriculumPath;
     uint32_t lastNumEvents = 0, lastNumSnaps = 0;
     bool replayPending = false;              // mpenv_set_replay_log() data waiting for the next step
 };
@@ -367,6 +368,8 @@ int mpenv_create(const mpenv_config *cfg, mpenv_handle **out)
     if (h->eventLog) h->eventDir = cfg->event_log_dir;
     if (h->recordLog) h->recordPath = cfg->record_log_path;
     if (h->replayLog) h->replayPath = cfg->replay_log_path;
+    if (cfg->curriculum_data_path) h->curriculumPath = cfg->curriculum_data_path;
+    h->cfg.curriculum_data_path = cfg->curriculum_data_path ? h->curriculumPath.c_str() : nullptr;
     h->cfg.event_log_dir = h->eventLog ? h->eventDir.c_str() : nullptr;
     h->cfg.record_log_path = h->recordLog ? h->recordPath.c_str() : nullptr;
     h->cfg.replay_log_path = h->replayLog ? h->replayPath.c_str() : nullptr;
@@ -424,6 +427,26 @@ int mpenv_create(const mpenv_config *cfg, mpenv_handle **out)
     ka.ctx.cfg.eventLog = h->eventLog ? 1 : 0;
     ka.ctx.cfg.recordLog = h->recordLog ? 1 : 0;
     ka.ctx.cfg.replayLog = h->replayLog ? 1 : 0;
+
+    // trajectory curriculum (mgr.cpp:1424-1441, 1643-1650)
+    if (cfg->curriculum_data_path) {
+        FILE *f = fopen(h->curriculumPath.c_str(), "rb");
+        if (!f) { h->error = "failed to open curriculum data " + h->curriculumPath; return bail(MPENV_ERR_IO); }
+        std::vector<char> data;
+        char chunk[65536];
+        size_t got;
+        while ((got = fread(chunk, 1, sizeof(chunk), f)) > 0) data.insert(data.end(), chunk, chunk + got);
+        fclose(f);
+        const size_t n = data.size() / sizeof(CurriculumSnapshot);
+        if (n > 0) {
+            CurriculumSnapshot *dev = nullptr;
+            if (!devAlloc((void **)&dev, n * sizeof(CurriculumSnapshot))) return bail(MPENV_ERR_CUDA);
+            MP_CREATE(cudaMemcpyAsync(dev, data.data(), n * sizeof(CurriculumSnapshot), cudaMemcpyHostToDevice, h->stream));
+            MP_CREATE(cudaStreamSynchronize(h->stream));     // `data` is pageable and about to go away
+            ka.ctx.p.curriculum = dev;
+        }
+        ka.ctx.cfg.numCurriculumSnapshots = (int32_t)n;
+    }
 
     // logs: files as the reference opens them (mgr.cpp:200-231; FATAL there, an error here)
     {

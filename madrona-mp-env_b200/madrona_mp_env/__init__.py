@@ -53,7 +53,7 @@ class _Config(C.Structure):
                 ("policy_history_size", C.c_uint32), ("scene_dir", C.c_char_p),
                 ("world_id_offset", C.c_uint32), ("enable_full_team", C.c_uint32),
                 ("event_log_dir", C.c_char_p), ("record_log_path", C.c_char_p),
-                ("replay_log_path", C.c_char_p)]
+                ("replay_log_path", C.c_char_p), ("curriculum_data_path", C.c_char_p)]
 
 
 class _TensorDesc(C.Structure):
@@ -138,8 +138,6 @@ class SimManager:
                  curriculum_data_path=None, world_id_offset=0, enable_full_team=True):
         if int(exec_mode) != int(ExecMode.CUDA):
             raise ValueError("madrona_mp_env (B200): only ExecMode.CUDA exists; there is no CPU path")
-        if curriculum_data_path is not None:
-            raise NotImplementedError("curriculum_data_path: the trajectory curriculum is outside this build's scope")
         if train_flank:
             raise NotImplementedError("train_flank (RewardMode::Flank) is outside this build's scope")
         self._lib = _load()
@@ -149,7 +147,8 @@ class SimManager:
         cfg = _Config(int(gpu_id), int(num_worlds), int(rand_seed), int(bool(auto_reset)),
                       int(sim_flags), int(task_type), int(team_size), int(num_pbt_policies),
                       int(policy_history_size), self._scene, int(world_id_offset), int(enable_full_team),
-                      enc(event_log_path), enc(record_log_path), enc(replay_log_path))
+                      enc(event_log_path), enc(record_log_path), enc(replay_log_path),
+                      enc(curriculum_data_path))
         self._h = C.c_void_p()
         rc = self._lib.mpenv_create(C.byref(cfg), C.byref(self._h))
         if rc != 0:

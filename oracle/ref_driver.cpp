@@ -62,6 +62,8 @@ struct RefConfig {
     uint32_t enableEventLog;  // TaskConfig::eventGlobalState (mgr.cpp:1227, 1777)
     uint32_t enableRecordLog; // TaskConfig::recordLog (mgr.cpp:1774)
     uint32_t enableReplayLog; // TaskConfig::replayLog (mgr.cpp:1775)
+    uint32_t numCurriculumSnapshots;      // TrajectoryCurriculum (mgr.cpp:1419-1441)
+    const void *curriculumSnapshots;      // numCurriculumSnapshots x sizeof(CurriculumSnapshot), copied
 };
 
 struct RefSim {
@@ -84,6 +86,7 @@ struct RefSim {
     SpawnCurriculum spawnCurriculum;
     EventLogGlobalState eventGlobal { 0, 0 };
     std::vector<StepLog> recordLog, replayLog;
+    std::vector<CurriculumSnapshot> curriculum;
     std::string error;
 };
 
@@ -343,7 +346,13 @@ void * ref_create(const RefConfig *cfg, const char *scene_dir,
     tc.numWeaponTypes = 1;
     tc.weaponTypeStats = &s->weapon;
     tc.trainControl = &s->trainCtrl;
-    tc.trajectoryCurriculum = TrajectoryCurriculum { 0, nullptr };
+    static_assert(sizeof(CurriculumSnapshot) == 176);
+    if (cfg->numCurriculumSnapshots > 0 && cfg->curriculumSnapshots) {
+        s->curriculum.resize(cfg->numCurriculumSnapshots);
+        memcpy(s->curriculum.data(), cfg->curriculumSnapshots, sizeof(CurriculumSnapshot) * cfg->numCurriculumSnapshots);
+    }
+    tc.trajectoryCurriculum = TrajectoryCurriculum { (i32)s->curriculum.size(),
+                                                     s->curriculum.empty() ? nullptr : s->curriculum.data() };
     tc.policyWeights = nullptr;
 
     // The registry is process-global (type ids are static); registering the

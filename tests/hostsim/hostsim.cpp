@@ -24,6 +24,7 @@ struct HostSim {
     MapConsts consts;
     Ctx ctx;
     std::vector<void *> allocs;
+    std::vector<CurriculumSnapshot> curriculum;
     uint32_t numWorlds;
     bool fullTeam;
 };
@@ -62,6 +63,8 @@ struct HostSimConfig {
     int32_t autoReset;
     uint32_t simFlags, worldIDOffset, enableFullTeam;
     uint32_t enableEventLog, enableRecordLog, enableReplayLog;
+    uint32_t numCurriculumSnapshots;
+    const void *curriculumSnapshots;
 };
 
 void *hostsim_create(const HostSimConfig *cfg, const char *scene_dir)
@@ -97,6 +100,12 @@ void *hostsim_create(const HostSimConfig *cfg, const char *scene_dir)
         void *mem = calloc(bufferRows(table[i], cfg->numWorlds), table[i].rowBytes);
         *bufferSlot(&c.p, table[i]) = mem;
         s->allocs.push_back(mem);
+    }
+    if (cfg->numCurriculumSnapshots > 0 && cfg->curriculumSnapshots) {
+        s->curriculum.resize(cfg->numCurriculumSnapshots);
+        memcpy(s->curriculum.data(), cfg->curriculumSnapshots, sizeof(CurriculumSnapshot) * cfg->numCurriculumSnapshots);
+        c.p.curriculum = s->curriculum.data();
+        c.cfg.numCurriculumSnapshots = (int32_t)cfg->numCurriculumSnapshots;
     }
     // mgr.cpp:1397-1413
     c.p.trainCtrl->evalMode = (cfg->simFlags & kFlagSimEvalMode) ? 1 : 0;

@@ -260,7 +260,8 @@ class RefConfig(C.Structure):
                 ("numPBTPolicies", C.c_uint32), ("policyHistorySize", C.c_uint32),
                 ("worldIDOffset", C.c_uint32), ("numThreads", C.c_uint32),
                 ("enableEventLog", C.c_uint32), ("enableRecordLog", C.c_uint32),
-                ("enableReplayLog", C.c_uint32)]
+                ("enableReplayLog", C.c_uint32), ("numCurriculumSnapshots", C.c_uint32),
+                ("curriculumSnapshots", C.c_void_p)]
 
 
 # Log record layouts (reference types.hpp:574-634, 729-760; csrc/mp_defs.h).
@@ -275,7 +276,20 @@ AGENT_LOG_DT = np.dtype([("position", "<f4", (3,)), ("aim", "<f4", (6,)), ("hp",
                          ("standState", "<i4", (3,)), ("shotAgentIdx", "<i4"), ("firedShotT", "<f4"),
                          ("wasKilled", "u1"), ("successfullKill", "u1"), ("pad", "u1", (2,))])
 STEP_LOG_DT = np.dtype([("agentData", AGENT_LOG_DT, (12,)), ("curStep", "<i4")])
+CURRICULUM_DT = np.dtype([("step", "<u2"), ("curZone", "u1"), ("curZoneController", "i1"),
+                          ("zoneStepsRemaining", "<u2"), ("stepsUntilPoint", "<u2"),
+                          ("players", PLAYER_SNAP_DT, (12,))])
 assert EVENT_DT.itemsize == 24 and SNAP_DT.itemsize == 192 and STEP_LOG_DT.itemsize == 868
+assert CURRICULUM_DT.itemsize == 176
+
+
+def curriculum_from_step_snapshots(snaps):
+    """CurriculumSnapshot records (types.hpp:816-819) from PackedStepSnapshot records: the
+    body after the 16-byte {numEvents, eventMask, matchID} header (what
+    build_trajectory_curriculum.cpp:9-60 reassembles from the analytics DB)."""
+    raw = np.ascontiguousarray(snaps).view(np.uint8).reshape(len(snaps), SNAP_DT.itemsize)
+    return np.ascontiguousarray(raw[:, 16:]).view(CURRICULUM_DT).reshape(len(snaps))
+
 EV_CAPTURE, EV_RELOAD, EV_KILL, EV_PLAYER_SHOT = 1, 2, 4, 8
 
 
@@ -337,7 +351,7 @@ class Oracle(_SimBase):
 
     def __init__(self, num_worlds, rand_seed=10, auto_reset=False, sim_flags=0, det=True,
                  world_id_offset=0, num_threads=1, scene=SCENE, bvh=None, event_log=False,
-                 record_log=False, replay_log=False):
+                 record_log=False, replay_log=False, curriculum=None):
         build_oracle()
         self.lib = C.CDLL(REF_DET_SO if det else REF_SO)
         L = self.lib
@@ -364,7 +378,9 @@ class Oracle(_SimBase):
         v20 = np.zeros((verts.shape[0], 5), dtype=np.float32)     # BVHVertex {pos, uv}
         v20[:, :3] = verts
         cfg = RefConfig(num_worlds, rand_seed, int(auto_reset), sim_flags, 2, 6, 0, 1,
-                        world_id_offset, num_threads, int(event_log), int(record_log), int(replay_log))
+                        world_id_offset, num_threads, int(event_log), int(record_log), int(replay_log),
+                        0 if curriculum is None else len(curriculum),
+                        None if curriculum is None else np.ascontiguousarray(curriculum).ctypes.data)
         L.ref_read_event_log.restype = C.c_int64
         L.ref_read_event_log.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint64]
         L.ref_event_log_counts.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
@@ -460,14 +476,16 @@ class HostSimConfig(C.Structure):
     _fields_ = [("numWorlds", C.c_uint32), ("randSeed", C.c_uint32), ("autoReset", C.c_int32),
                 ("simFlags", C.c_uint32), ("worldIDOffset", C.c_uint32), ("enableFullTeam", C.c_uint32),
                 ("enableEventLog", C.c_uint32), ("enableRecordLog", C.c_uint32),
-                ("enableReplayLog", C.c_uint32)]
+                ("enableReplayLog", C.c_uint32), ("numCurriculumSnapshots", C.c_uint32),
+                ("curriculumSnapshots", C.c_void_p)]
 
 
 class HostSim(_SimBase):
     """Device stage functions compiled for the host (tests only)."""
 
     def __init__(self, num_worlds, rand_seed=10, auto_reset=False, sim_flags=0, world_id_offset=0,
-                 full_team=True, scene=SCENE, event_log=False, record_log=False, replay_log=False):
+                 full_team=True, scene=SCENE, event_log=False, record_log=False, replay_log=False,
+                 curriculum=None):
         self.lib = C.CDLL(build_hostsim())
         L = self.lib
         L.hostsim_create.restype = C.c_void_p
@@ -481,7 +499,9 @@ class HostSim(_SimBase):
         L.hostsim_sphere_cast.restype = C.c_float
         L.hostsim_sphere_cast.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_float, C.c_void_p]
         cfg = HostSimConfig(num_worlds, rand_seed, int(auto_reset), sim_flags, world_id_offset,
-                            int(full_team), int(event_log), int(record_log), int(replay_log))
+                            int(full_team), int(event_log), int(record_log), int(replay_log),
+                            0 if curriculum is None else len(curriculum),
+                            None if curriculum is None else np.ascontiguousarray(curriculum).ctypes.data)
         L.hostsim_read_event_log.restype = C.c_int64
         L.hostsim_read_event_log.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint64]
         L.hostsim_record_log.restype = C.c_void_p
@@ -644,7 +664,7 @@ class MpenvConfig(C.Structure):
                 ("policy_history_size", C.c_uint32), ("scene_dir", C.c_char_p),
                 ("world_id_offset", C.c_uint32), ("enable_full_team", C.c_uint32),
                 ("event_log_dir", C.c_char_p), ("record_log_path", C.c_char_p),
-                ("replay_log_path", C.c_char_p)]
+                ("replay_log_path", C.c_char_p), ("curriculum_data_path", C.c_char_p)]
 
 
 class TensorDesc(C.Structure):
@@ -684,13 +704,15 @@ class GpuSim(_SimBase):
     """The product: libmpenv_b200.so through its C ABI, host buffers in and out."""
 
     def __init__(self, num_worlds, rand_seed=10, auto_reset=False, sim_flags=0, world_id_offset=0,
-                 full_team=True, scene=SCENE, gpu_id=0, event_log=False, record_log=False, replay_log=False):
+                 full_team=True, scene=SCENE, gpu_id=0, event_log=False, record_log=False, replay_log=False,
+                 curriculum_path=None):
         """event_log / record_log / replay_log: False = off, True = in memory only,
         a path = the reference's files (event_log: directory)."""
         self.lib = load_product()
         self._scene = scene.encode()
         path = lambda v: None if v is False or v is None else (b"" if v is True else str(v).encode())
-        self._log_paths = [path(event_log), path(record_log), path(replay_log)]
+        self._log_paths = [path(event_log), path(record_log), path(replay_log),
+                           None if curriculum_path is None else str(curriculum_path).encode()]
         cfg = MpenvConfig(gpu_id, num_worlds, rand_seed, int(auto_reset), sim_flags, 2, 6, 0, 1,
                           self._scene, world_id_offset, int(full_team), *self._log_paths)
         self.h = C.c_void_p()

@@ -125,3 +125,33 @@ def test_python_manager_logs(tmp_path):
     assert os.path.getsize(os.path.join(tmp_path, "steps.bin")) == 5 * W * S.SNAP_DT.itemsize
     assert os.path.getsize(rec) == 5 * W * S.STEP_LOG_DT.itemsize
     assert os.path.getsize(os.path.join(tmp_path, "events.bin")) % S.EVENT_DT.itemsize == 0
+
+
+def test_trajectory_curriculum_gpu(tmp_path, built):
+    """curriculum_data_path (mgr.cpp:1424-1441) -> level_gen.cpp:498-581 on the device."""
+    from test_logs_host import _make_curriculum
+    cur = _make_curriculum(built)
+    path = os.path.join(tmp_path, "curriculum.bin")
+    cur.tofile(path)
+    W = 8
+    for flags in (0, 128):
+        gpu = S.GpuSim(W, auto_reset=True, sim_flags=flags, curriculum_path=path)
+        orc = S.Oracle(W, auto_reset=True, det=True, sim_flags=flags, curriculum=cur)
+        try:
+            gpu.init(); orc.init()
+            assert sum(orc.world_state(w)["cur_step"] > 0 for w in range(W)) > 0 or flags
+            for s in range(60):
+                d, a = S.random_actions(s, W)
+                for sim in (gpu, orc):
+                    sim.set_actions(d, a)
+                    if s % 20 == 10:
+                        sim.set_export("reset", np.ones((W, 1), np.int32))
+                    sim.step()
+                for name in S.STEP_OUTPUTS:
+                    x, y = gpu.export(name), orc.export(name)
+                    assert np.array_equal(x.view(np.int32), y.view(np.int32)), f"flags {flags} step {s}: {name}"
+                for w in range(W):
+                    dd = S.diff_world_state(gpu.world_state(w), orc.world_state(w), skip=("reloaded_full_mag",))
+                    assert not dd, f"flags {flags} step {s} world {w}: {dd[:6]}"
+        finally:
+            gpu.close(); orc.close()
