@@ -238,6 +238,17 @@ int mpenv_map_info(const mpenv_map *m, mpenv_map_info_t *info);
 const void *mpenv_map_nodes(const mpenv_map *m);
 /* (num_tris + 1) x 3 x 3 floats: de-indexed triangle positions in leaf order */
 const float *mpenv_map_verts(const mpenv_map *m);
+/* Navmesh + A* next-triangle table of the scripted bot (policy id -1): the data the
+ * reference builds in Impl::init (mgr.cpp:1300-1330: importNavmesh, vertex de-duplication,
+ * Navmesh::initFromPolygons, buildAStarLookup mgr.cpp:946-1211).  Pointers are owned by `m`. */
+typedef struct mpenv_navmesh_t {
+    uint32_t num_verts, num_tris;
+    const float *verts;            /* num_verts x 3 */
+    const uint32_t *tri_indices;   /* num_tris x 3 */
+    const int32_t *tri_adjacency;  /* num_tris x 3, -1 = border */
+    const uint32_t *astar_lookup;  /* num_tris x num_tris: next triangle [start][goal], 0xFFFFFFFF = none */
+} mpenv_navmesh_t;
+int mpenv_map_navmesh(const mpenv_map *m, mpenv_navmesh_t *out);
 const char *mpenv_map_last_error(void);
 
 #ifdef __cplusplus

@@ -349,6 +349,10 @@ bool loadMapAssets(const std::string &scene_dir, MapAssets *out, std::string *er
     if (!loadSpawns(scene_dir + "/spawns.bin", out, err)) return false;
     if (!loadZones(scene_dir + "/zones.bin", out, err)) return false;
     buildMeshBVH(tris, out);
+    // The reference requires navmesh.bin (map_importer.cpp:426 asserts); here it is
+    // needed only when an agent's policy id is -1 (the A* bot).
+    std::string nav_err;
+    out->hasNav = loadNavmesh(scene_dir + "/navmesh.bin", &out->nav, &nav_err);
     return true;
 }
 

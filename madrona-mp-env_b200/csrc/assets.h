@@ -13,6 +13,7 @@
 #include <vector>
 
 #include "mp_defs.h"
+#include "navmesh.h"
 
 namespace mpenv {
 
@@ -28,6 +29,9 @@ struct MapAssets {
     std::vector<Spawn> aSpawns, bSpawns, respawns;
     std::vector<AABB> zoneBoxes;
     std::vector<float> zoneRots;
+    // navmesh + A* table for the scripted bot (optional: navmesh.bin may be absent)
+    NavmeshAssets nav;
+    bool hasNav = false;
 };
 
 // Loads <scene_dir>/{collisions,spawns,zones}.bin and builds the BVH.

@@ -55,6 +55,20 @@ int mpenv_map_info(const mpenv_map *m, mpenv_map_info_t *info)
 const void *mpenv_map_nodes(const mpenv_map *m) { return m ? m->assets.nodes.data() : nullptr; }
 const float *mpenv_map_verts(const mpenv_map *m) { return m ? (const float *)m->assets.verts.data() : nullptr; }
 
+int mpenv_map_navmesh(const mpenv_map *m, mpenv_navmesh_t *out)
+{
+    if (!m || !out) return MPENV_ERR_INVALID;
+    if (!m->assets.hasNav) { g_map_error = "navmesh.bin not found in the scene directory"; return MPENV_ERR_IO; }
+    const NavmeshAssets &n = m->assets.nav;
+    out->num_verts = (uint32_t)n.verts.size();
+    out->num_tris = n.numTris();
+    out->verts = (const float *)n.verts.data();
+    out->tri_indices = n.tris.data();
+    out->tri_adjacency = n.adjacency.data();
+    out->astar_lookup = n.lookup.data();
+    return MPENV_OK;
+}
+
 }  // extern "C"
 
 namespace mpenv {

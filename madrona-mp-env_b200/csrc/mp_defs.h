@@ -287,6 +287,14 @@ struct BVHView {
     uint32_t numNodes, numTris;
 };
 
+// Navmesh + A* next-triangle table for the scripted bot (LevelData, types.hpp:136-143).
+struct NavView {
+    const Vec3 *verts;
+    const uint32_t *tris;      // 3 per triangle
+    const uint32_t *lookup;    // numTris x numTris
+    uint32_t numTris;
+};
+
 struct MapConsts {
     AABB worldBounds;
     float maxDist;                      // Sim::maxDist (sim.cpp:5855)

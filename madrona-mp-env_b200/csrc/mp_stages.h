@@ -18,6 +18,7 @@ struct Ctx {
     const MapConsts *mc;
     BVHView bvh;
     SimPtrs p;
+    NavView nav;             // numTris == 0: no navmesh loaded (bots stand still)
 };
 
 MP_HD int teamOf(int a) { return a / kTeamSize; }
@@ -254,6 +255,10 @@ MP_HD void fallSystem(const BVHView &bvh, Vec3 pos, MoveState &move, float alive
     move.newPos = new_pos;
 }
 
+}  // namespace mpenv
+#include "mp_stages_bot.h"
+namespace mpenv {
+
 // Per-agent fusion of Step-graph nodes 3-8 (sim.cpp:5403-5460): movement,
 // both aim systems, applyVelocity, updateMoveState, fall, post-fall update.
 // No cross-agent reads.
@@ -269,6 +274,7 @@ MP_HD void stageMove(const Ctx &c, int idx)
     Aim aim = p.aim[idx];
     Vec3 pos = p.pos[idx];
 
+    stageBot(c, idx);            // policy id -1: plan + apply the scripted bot's action rows
     movementSystem(p.actDiscrete[idx], rot, vel, alive, combat, stand, move);
     aimSystems(p.actAim[idx], p.actDiscreteAim[idx], rot, aim, alive);
     applyVelocitySystem(c.bvh, pos, vel, stand.cur, move);

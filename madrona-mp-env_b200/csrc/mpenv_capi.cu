@@ -428,6 +428,19 @@ int mpenv_create(const mpenv_config *cfg, mpenv_handle **out)
     ka.ctx.cfg.recordLog = h->recordLog ? 1 : 0;
     ka.ctx.cfg.replayLog = h->replayLog ? 1 : 0;
 
+    // navmesh + A* table for the scripted bot (LevelData, sim.cpp:5895-5898)
+    if (h->assets.hasNav) {
+        const NavmeshAssets &nav = h->assets.nav;
+        Vec3 *dv = nullptr; uint32_t *dt = nullptr, *dl = nullptr;
+        if (!devAlloc((void **)&dv, nav.verts.size() * sizeof(Vec3)) || !devAlloc((void **)&dt, nav.tris.size() * 4) ||
+            !devAlloc((void **)&dl, nav.lookup.size() * 4))
+            return bail(MPENV_ERR_CUDA);
+        MP_CREATE(cudaMemcpyAsync(dv, nav.verts.data(), nav.verts.size() * sizeof(Vec3), cudaMemcpyHostToDevice, h->stream));
+        MP_CREATE(cudaMemcpyAsync(dt, nav.tris.data(), nav.tris.size() * 4, cudaMemcpyHostToDevice, h->stream));
+        MP_CREATE(cudaMemcpyAsync(dl, nav.lookup.data(), nav.lookup.size() * 4, cudaMemcpyHostToDevice, h->stream));
+        ka.ctx.nav.verts = dv; ka.ctx.nav.tris = dt; ka.ctx.nav.lookup = dl; ka.ctx.nav.numTris = nav.numTris();
+    }
+
     // trajectory curriculum (mgr.cpp:1424-1441, 1643-1650)
     if (cfg->curriculum_data_path) {
         FILE *f = fopen(h->curriculumPath.c_str(), "rb");

@@ -64,6 +64,14 @@ struct RefConfig {
     uint32_t enableReplayLog; // TaskConfig::replayLog (mgr.cpp:1775)
     uint32_t numCurriculumSnapshots;      // TrajectoryCurriculum (mgr.cpp:1419-1441)
     const void *curriculumSnapshots;      // numCurriculumSnapshots x sizeof(CurriculumSnapshot), copied
+    // Navmesh + A* table (LevelData, types.hpp:136-143), handed in by the caller like the BVH:
+    // madrona::Navmesh::initFromPolygons and meshoptimizer are not vendored, and
+    // buildAStarLookup lives in mgr.cpp, which cannot be compiled here.  All copied.
+    uint32_t numNavVerts, numNavTris;
+    const float *navVerts;                // numNavVerts x 3
+    const uint32_t *navTriIndices;        // numNavTris x 3
+    const int32_t *navTriAdjacency;       // numNavTris x 3
+    const uint32_t *navLookup;            // numNavTris x numNavTris
 };
 
 struct RefSim {
@@ -87,6 +95,8 @@ struct RefSim {
     EventLogGlobalState eventGlobal { 0, 0 };
     std::vector<StepLog> recordLog, replayLog;
     std::vector<CurriculumSnapshot> curriculum;
+    std::vector<math::Vector3> navVerts;
+    std::vector<uint32_t> navTris, navAdj, navLookup;
     std::string error;
 };
 
@@ -310,6 +320,22 @@ void * ref_create(const RefConfig *cfg, const char *scene_dir,
     zones.numZones = (uint32_t)s->zoneAABBs.size();
 
     Navmesh navmesh {};
+    AStarLookup astar { nullptr };
+    if (cfg->numNavTris > 0 && cfg->navVerts && cfg->navTriIndices && cfg->navLookup) {
+        s->navVerts.resize(cfg->numNavVerts);
+        memcpy(s->navVerts.data(), cfg->navVerts, sizeof(float) * 3 * cfg->numNavVerts);
+        s->navTris.assign(cfg->navTriIndices, cfg->navTriIndices + 3 * (size_t)cfg->numNavTris);
+        s->navAdj.resize(3 * (size_t)cfg->numNavTris);
+        if (cfg->navTriAdjacency) memcpy(s->navAdj.data(), cfg->navTriAdjacency, 4 * s->navAdj.size());
+        s->navLookup.assign(cfg->navLookup, cfg->navLookup + (size_t)cfg->numNavTris * cfg->numNavTris);
+        navmesh.vertices = s->navVerts.data();
+        navmesh.triIndices = s->navTris.data();
+        navmesh.triAdjacency = s->navAdj.data();
+        navmesh.triSampleCDF = nullptr;
+        navmesh.numVerts = cfg->numNavVerts;
+        navmesh.numTris = cfg->numNavTris;
+        astar.data = s->navLookup.data();
+    }
 
     // mgr.cpp:1752-1785
     TaskConfig &tc = s->taskCfg;
@@ -326,7 +352,7 @@ void * ref_create(const RefConfig *cfg, const char *scene_dir,
     tc.staticMeshes = &s->bvh;
     tc.numStaticMeshes = 1;
     tc.navmesh = navmesh;
-    tc.aStarLookup = AStarLookup { nullptr };
+    tc.aStarLookup = astar;
     tc.standardSpawns = spawns;
     tc.spawnCurriculum = s->spawnCurriculum;
     tc.zones = zones;

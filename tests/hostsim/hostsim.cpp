@@ -94,6 +94,12 @@ void *hostsim_create(const HostSimConfig *cfg, const char *scene_dir)
     c.bvh.rootAABB = s->assets.rootAABB;
     c.bvh.numNodes = (uint32_t)s->assets.nodes.size();
     c.bvh.numTris = s->assets.numTris;
+    if (s->assets.hasNav) {
+        c.nav.verts = s->assets.nav.verts.data();
+        c.nav.tris = s->assets.nav.tris.data();
+        c.nav.lookup = s->assets.nav.lookup.data();
+        c.nav.numTris = s->assets.nav.numTris();
+    }
     int n;
     const BufferDesc *table = bufferTable(&n);
     for (int i = 0; i < n; i++) {

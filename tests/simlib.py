@@ -201,7 +201,8 @@ def build_hostsim():
         _run(["g++", "-std=c++17", "-O2", "-march=x86-64-v3", "-ffp-contract=off", "-fno-fast-math",
               "-fPIC", "-shared", "-o", HOSTSIM_SO,
               os.path.join(ROOT, "tests", "hostsim", "hostsim.cpp"),
-              os.path.join(CSRC, "assets.cpp"), os.path.join(CSRC, "map_capi.cpp")])
+              os.path.join(CSRC, "assets.cpp"), os.path.join(CSRC, "map_capi.cpp"),
+              os.path.join(CSRC, "navmesh.cpp")])
     return HOSTSIM_SO
 
 
@@ -253,6 +254,33 @@ def load_map(lib, scene=SCENE):
     return nodes, verts, info
 
 
+class NavmeshDesc(C.Structure):
+    _fields_ = [("num_verts", C.c_uint32), ("num_tris", C.c_uint32), ("verts", C.c_void_p),
+                ("tri_indices", C.c_void_p), ("tri_adjacency", C.c_void_p), ("astar_lookup", C.c_void_p)]
+
+
+def load_navmesh(lib, scene=SCENE):
+    """(verts f32[nv,3], tris u32[nt,3], adjacency i32[nt,3], lookup u32[nt,nt]) from the
+    mpenv_map_navmesh C ABI of `lib`."""
+    lib.mpenv_map_load.argtypes = [C.c_char_p, C.POINTER(C.c_void_p)]
+    lib.mpenv_map_navmesh.argtypes = [C.c_void_p, C.POINTER(NavmeshDesc)]
+    lib.mpenv_map_free.argtypes = [C.c_void_p]
+    lib.mpenv_map_last_error.restype = C.c_char_p
+    m = C.c_void_p()
+    rc = lib.mpenv_map_load(scene.encode(), C.byref(m))
+    if rc != 0:
+        raise RuntimeError(f"mpenv_map_load failed ({rc}): {lib.mpenv_map_last_error().decode()}")
+    d = NavmeshDesc()
+    rc = lib.mpenv_map_navmesh(m, C.byref(d))
+    if rc != 0:
+        raise RuntimeError(f"mpenv_map_navmesh failed ({rc}): {lib.mpenv_map_last_error().decode()}")
+    arr = lambda ptr, ct, shape: np.ctypeslib.as_array(C.cast(ptr, C.POINTER(ct)), shape=shape).copy()
+    out = (arr(d.verts, C.c_float, (d.num_verts, 3)), arr(d.tri_indices, C.c_uint32, (d.num_tris, 3)),
+           arr(d.tri_adjacency, C.c_int32, (d.num_tris, 3)), arr(d.astar_lookup, C.c_uint32, (d.num_tris, d.num_tris)))
+    lib.mpenv_map_free(m)
+    return out
+
+
 # ------------------------------------------------------------------- oracle
 class RefConfig(C.Structure):
     _fields_ = [("numWorlds", C.c_uint32), ("randSeed", C.c_uint32), ("autoReset", C.c_int32),
@@ -261,7 +289,9 @@ class RefConfig(C.Structure):
                 ("worldIDOffset", C.c_uint32), ("numThreads", C.c_uint32),
                 ("enableEventLog", C.c_uint32), ("enableRecordLog", C.c_uint32),
                 ("enableReplayLog", C.c_uint32), ("numCurriculumSnapshots", C.c_uint32),
-                ("curriculumSnapshots", C.c_void_p)]
+                ("curriculumSnapshots", C.c_void_p), ("numNavVerts", C.c_uint32), ("numNavTris", C.c_uint32),
+                ("navVerts", C.c_void_p), ("navTriIndices", C.c_void_p), ("navTriAdjacency", C.c_void_p),
+                ("navLookup", C.c_void_p)]
 
 
 # Log record layouts (reference types.hpp:574-634, 729-760; csrc/mp_defs.h).
@@ -351,7 +381,7 @@ class Oracle(_SimBase):
 
     def __init__(self, num_worlds, rand_seed=10, auto_reset=False, sim_flags=0, det=True,
                  world_id_offset=0, num_threads=1, scene=SCENE, bvh=None, event_log=False,
-                 record_log=False, replay_log=False, curriculum=None):
+                 record_log=False, replay_log=False, curriculum=None, navmesh=True):
         build_oracle()
         self.lib = C.CDLL(REF_DET_SO if det else REF_SO)
         L = self.lib
@@ -381,6 +411,11 @@ class Oracle(_SimBase):
                         world_id_offset, num_threads, int(event_log), int(record_log), int(replay_log),
                         0 if curriculum is None else len(curriculum),
                         None if curriculum is None else np.ascontiguousarray(curriculum).ctypes.data)
+        if navmesh:
+            nv, nt, na, nl = self._nav = load_navmesh(C.CDLL(build_hostsim()), scene)
+            cfg.numNavVerts, cfg.numNavTris = len(nv), len(nt)
+            cfg.navVerts, cfg.navTriIndices = nv.ctypes.data, nt.ctypes.data
+            cfg.navTriAdjacency, cfg.navLookup = na.ctypes.data, nl.ctypes.data
         L.ref_read_event_log.restype = C.c_int64
         L.ref_read_event_log.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint64]
         L.ref_event_log_counts.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
