@@ -31,10 +31,21 @@ MP_HD GameEvent makeEvent(uint32_t type, uint64_t match_id, int32_t step, uint8_
     return e;
 }
 
+// Cold paths (event log, record / replay, trajectory curriculum) are compiled in only
+// when the template flag kCold is set: the kernels are instantiated both ways and the
+// host launches the lean variant when none of those features is configured, so the
+// plain step keeps its register budget (k_world: 56 vs 157 registers).
+MP_HD void logAgentEvent(const Ctx &c, int w, int a, int slot, uint32_t type, uint8_t b0, uint8_t b1)
+{
+    c.p.evAgent[(size_t)(w * kAgents + a) * kEventSlotsPerAgent + slot] =
+        makeEvent(type, matchIDOf(c, w), c.p.world[w].match.curStep, b0, b1, 0);
+}
+
 // ============================================================ stage: fire
 // fireSystem (sim.cpp:1443-1615).  Reads the world's 12 post-move positions
 // and the target's HP / respawn timer; writes only this agent's rows plus
 // DamageDealt[target][own team offset] (conflict-free: one slot per shooter).
+template <bool kCold = true>
 MP_HD void stageFire(const Ctx &c, int w, int a, const Vec3 *world_pos)
 {
     const SimPtrs &p = c.p;
@@ -45,10 +56,9 @@ MP_HD void stageFire(const Ctx &c, int w, int a, const Vec3 *world_pos)
     cs.firedShotT = -FLT_MAX;
     cs.reloadedFullMag = 0;
     const WeaponStats ws = c.mc->weapons[cs.weaponType];
-    const bool log_events = c.cfg.eventLog != 0;
-    GameEvent *ev = nullptr;
+    const bool log_events = kCold && c.cfg.eventLog != 0;
     if (log_events) {
-        ev = p.evAgent + (size_t)idx * kEventSlotsPerAgent;
+        GameEvent *ev = p.evAgent + (size_t)idx * kEventSlotsPerAgent;
         ev[0].type = kEvNone;
         ev[1].type = kEvNone;
     }
@@ -59,9 +69,7 @@ MP_HD void stageFire(const Ctx &c, int w, int a, const Vec3 *world_pos)
     const int32_t fire = p.actDiscrete[idx].fire;
     if (fire == 2) {
         // sim.cpp:1467-1476 (a reloading agent cannot also shoot this step, so slot 0 is free)
-        if (log_events)
-            ev[0] = makeEvent(kEvReload, matchIDOf(c, w), p.world[w].match.curStep, (uint8_t)a,
-                              (uint8_t)mag.numBullets, 0);
+        if (log_events) logAgentEvent(c, w, a, 0, kEvReload, (uint8_t)a, (uint8_t)mag.numBullets);
         if (mag.numBullets == ws.magSize) cs.reloadedFullMag = 1;
         mag.numBullets = ws.magSize;
         mag.isReloading = ws.reloadTime;
@@ -109,14 +117,10 @@ MP_HD void stageFire(const Ctx &c, int w, int a, const Vec3 *world_pos)
         cs.landedShotOn = hit_agent;
         float tgt_hp = p.hp[w * kAgents + hit_agent];
         // sim.cpp:1580-1609
-        if (log_events)
-            ev[0] = makeEvent(kEvPlayerShot, matchIDOf(c, w), p.world[w].match.curStep, (uint8_t)a,
-                              (uint8_t)hit_agent, 0);
+        if (log_events) logAgentEvent(c, w, a, 0, kEvPlayerShot, (uint8_t)a, (uint8_t)hit_agent);
         if (tgt_hp <= ws.dmgPerBullet) {
             cs.successfulKill = 1;
-            if (log_events)
-                ev[1] = makeEvent(kEvKill, matchIDOf(c, w), p.world[w].match.curStep, (uint8_t)a,
-                                  (uint8_t)hit_agent, 0);
+            if (log_events) logAgentEvent(c, w, a, 1, kEvKill, (uint8_t)a, (uint8_t)hit_agent);
         }
         p.dmg[(size_t)(w * kAgents + hit_agent) * kTeamSize + offsetOf(a)] = ws.dmgPerBullet;
     }
@@ -534,7 +538,39 @@ MP_HD void writePackedStepSnapshot(const Ctx &c, int w, bool captured)
     p.stepSnap[w] = s;
 }
 
+// The event-log tail of zoneMatchInfoSystem (sim.cpp:4592-4634): the Capture event and
+// the packed step snapshot.  evWorld[w]: the Capture event (type 0 = none); pad0 = 1
+// when a step snapshot was written.
+MP_HD void logWorldEvents(const Ctx &c, int w, bool new_captured)
+{
+    const SimPtrs &p = c.p;
+    const int base = w * kAgents;
+    const WorldState &ws = p.world[w];
+    const ZoneState &zs = ws.zone;
+    GameEvent cap = makeEvent(kEvNone, 0, 0, 0, 0, 0);
+    if (ws.matchIDValid && new_captured) {
+        Quat to_zone; AABB zbox;
+        zoneFrame(*c.mc, zs.curZone, &to_zone, &zbox);
+        uint32_t in_zone_mask = 0;
+        for (int i = 0; i < kAgents; i++) {
+            if (teamOf(i) != zs.curControllingTeam) continue;
+            Vec3 pos = p.pos[base + i];
+            pos.z += kStandHeight / 2.f;
+            if (!aabbContains(zbox, rotateVec(to_zone, pos))) continue;
+            in_zone_mask |= 1u << (uint32_t)i;
+        }
+        cap = makeEvent(kEvCapture, matchIDOf(c, w), ws.match.curStep, (uint8_t)zs.curZone,
+                        (uint8_t)zs.curControllingTeam, (uint16_t)in_zone_mask);
+    }
+    if (ws.matchIDValid) {
+        cap.pad0 = 1;
+        writePackedStepSnapshot(c, w, new_captured);
+    }
+    p.evWorld[w] = cap;
+}
+
 // zoneMatchInfoSystem (sim.cpp:4470-4673), Task::Zone.
+template <bool kCold = true>
 MP_HD void zoneMatchInfoSystem(const Ctx &c, int w)
 {
     const SimPtrs &p = c.p;
@@ -573,30 +609,7 @@ MP_HD void zoneMatchInfoSystem(const Ctx &c, int w)
         if (zs.isContested) st.contestedSteps += 1;
         if (new_captured) st.numSwaps += 1;
         updateFiltersState(c, w, cur_step);
-        // sim.cpp:4592-4634
-        if (c.cfg.eventLog) {
-            // evWorld[w]: the Capture event (type 0 = none); pad0 = 1 when a step snapshot was written
-            GameEvent cap = makeEvent(kEvNone, 0, 0, 0, 0, 0);
-            if (ws.matchIDValid && new_captured) {
-                Quat to_zone; AABB zbox;
-                zoneFrame(*c.mc, zs.curZone, &to_zone, &zbox);
-                uint32_t in_zone_mask = 0;
-                for (int i = 0; i < kAgents; i++) {
-                    if (teamOf(i) != zs.curControllingTeam) continue;
-                    Vec3 pos = p.pos[base + i];
-                    pos.z += kStandHeight / 2.f;
-                    if (!aabbContains(zbox, rotateVec(to_zone, pos))) continue;
-                    in_zone_mask |= 1u << (uint32_t)i;
-                }
-                cap = makeEvent(kEvCapture, matchIDOf(c, w), mi.curStep, (uint8_t)zs.curZone,
-                                (uint8_t)zs.curControllingTeam, (uint16_t)in_zone_mask);
-            }
-            if (ws.matchIDValid) {
-                cap.pad0 = 1;
-                writePackedStepSnapshot(c, w, new_captured);
-            }
-            p.evWorld[w] = cap;
-        }
+        if (kCold && c.cfg.eventLog) logWorldEvents(c, w, new_captured);      // sim.cpp:4592-4634
     }
     if (match_finished) {
         if (mr.teamObjectivePoints[0] > mr.teamObjectivePoints[1]) mr.winResult = 0;
@@ -784,7 +797,46 @@ MP_HD void teamAndFinalReward(const Ctx &c, int w)
     }
 }
 
+// level_gen.cpp:502-581: overwrite zone state, step counter and the agents with a
+// random recorded snapshot (teams mapped through teamA).
+MP_HD void restoreCurriculumSnapshot(const Ctx &c, int w)
+{
+    const SimPtrs &p = c.p;
+    const int base = w * kAgents;
+    WorldState &ws = p.world[w];
+    ZoneState &zs = ws.zone;
+    MatchInfo &mi = ws.match;
+    const int32_t snapshot_idx = rngI32(ws.baseRNG, 0, c.cfg.numCurriculumSnapshots);
+    const CurriculumSnapshot snap = p.curriculum[snapshot_idx];
+    zs.curZone = snap.matchState.curZone;
+    if (snap.matchState.curZoneController == -1) {
+        zs.curControllingTeam = -1;
+        zs.isCaptured = 0;
+    } else {
+        zs.isCaptured = 1;
+        zs.curControllingTeam = snap.matchState.curZoneController;
+        zs.stepsUntilPoint = snap.matchState.stepsUntilPoint;
+        zs.zoneStepsRemaining = snap.matchState.zoneStepsRemaining;
+    }
+    mi.curStep = snap.matchState.step;
+    for (int i = 0; i < kAgents; i++) {
+        const int a = mi.teamA == 0 ? i : (i < kAgents / 2 ? kAgents / 2 + i : i - kAgents / 2);
+        const int idx = base + a;
+        const PackedPlayerSnapshot ps = snap.players[i];
+        p.pos[idx] = v3((float)ps.pos[0], (float)ps.pos[1], (float)ps.pos[2]);
+        const Aim aim = computeAim((float)ps.yaw * kPi / 32768.f, (float)ps.pitch * kPi / 32768.f);
+        p.aim[idx] = aim;
+        p.rot[idx] = quatNormalize(angleAxis(aim.yaw, kUp()));
+        p.hp[idx] = (float)ps.hp;
+        Magazine mag; mag.numBullets = ps.magNumBullets; mag.isReloading = ps.isReloading;
+        p.mag[idx] = mag;
+        if (ps.flags & (1u << 2)) { StandState st; st.cur = 1; st.tgt = 1; st.transition = 0; p.stand[idx] = st; }
+        if (ps.flags & (1u << 3)) { StandState st; st.cur = 2; st.tgt = 2; st.transition = 0; p.stand[idx] = st; }
+    }
+}
+
 // initWorld (sim.cpp:732-833) + resetPersistentEntities (level_gen.cpp:330-582)
+template <bool kCold = true>
 MP_HD void initWorld(const Ctx &c, int w, bool triggered_reset)
 {
     const SimPtrs &p = c.p;
@@ -890,41 +942,15 @@ MP_HD void initWorld(const Ctx &c, int w, bool triggered_reset)
     }
     // Trajectory curriculum (level_gen.cpp:498-581): half of the episodes (not in
     // eval mode) start from a recorded mid-match snapshot instead of the spawn state.
-    if (c.cfg.numCurriculumSnapshots > 0 && rngUniform(base_rng) < 0.5f && !tc.evalMode) {
-        const int32_t snapshot_idx = rngI32(base_rng, 0, c.cfg.numCurriculumSnapshots);
-        const CurriculumSnapshot snap = p.curriculum[snapshot_idx];
-        zs.curZone = snap.matchState.curZone;
-        if (snap.matchState.curZoneController == -1) {
-            zs.curControllingTeam = -1;
-            zs.isCaptured = 0;
-        } else {
-            zs.isCaptured = 1;
-            zs.curControllingTeam = snap.matchState.curZoneController;
-            zs.stepsUntilPoint = snap.matchState.stepsUntilPoint;
-            zs.zoneStepsRemaining = snap.matchState.zoneStepsRemaining;
-        }
-        mi.curStep = snap.matchState.step;
-        for (int i = 0; i < kAgents; i++) {
-            const int a = mi.teamA == 0 ? i : (i < kAgents / 2 ? kAgents / 2 + i : i - kAgents / 2);
-            const int idx = base + a;
-            const PackedPlayerSnapshot ps = snap.players[i];
-            p.pos[idx] = v3((float)ps.pos[0], (float)ps.pos[1], (float)ps.pos[2]);
-            const Aim aim = computeAim((float)ps.yaw * kPi / 32768.f, (float)ps.pitch * kPi / 32768.f);
-            p.aim[idx] = aim;
-            p.rot[idx] = quatNormalize(angleAxis(aim.yaw, kUp()));
-            p.hp[idx] = (float)ps.hp;
-            Magazine mag; mag.numBullets = ps.magNumBullets; mag.isReloading = ps.isReloading;
-            p.mag[idx] = mag;
-            if (ps.flags & (1u << 2)) { StandState st; st.cur = 1; st.tgt = 1; st.transition = 0; p.stand[idx] = st; }
-            if (ps.flags & (1u << 3)) { StandState st; st.cur = 2; st.tgt = 2; st.transition = 0; p.stand[idx] = st; }
-        }
-    }
+    if (kCold && c.cfg.numCurriculumSnapshots > 0 && rngUniform(base_rng) < 0.5f && !tc.evalMode)
+        restoreCurriculumSnapshot(c, w);
     // back in initWorld (sim.cpp:829-832)
     for (int t = 0; t < 2; t++) { ws.filtersActive[t] = 0; ws.filtersLastMatchedStep[t] = 0; }
     ws.matchIDValid = 1;
 }
 
 // resetSystem (sim.cpp:835-872)
+template <bool kCold = true>
 MP_HD void resetSystem(const Ctx &c, int w)
 {
     const SimPtrs &p = c.p;
@@ -943,7 +969,7 @@ MP_HD void resetSystem(const Ctx &c, int w)
                 p.worldCurriculum[w] = 1;
             }
         }
-        initWorld(c, w, force_reset == 1);
+        initWorld<kCold>(c, w, force_reset == 1);
     }
 }
 

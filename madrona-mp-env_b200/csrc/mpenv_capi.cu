@@ -78,6 +78,7 @@ struct mpenv_handle {
     StepLog *hostReplay = nullptr;           // pinned
     std::string curriculumPath;
     uint32_t lastNumEvents = 0, lastNumSnaps = 0;
+    bool cold = false;                       // any log / replay / curriculum feature on: the kCold kernel variants
     bool replayPending = false;              // mpenv_set_replay_log() data waiting for the next step
 };
 
@@ -167,13 +168,17 @@ uint32_t launchStep(mpenv_handle *h, cudaStream_t s, bool fork)
     uint32_t n = 0;
     if (!h->replayLog) {
         k_move<<<h->gridMove, 128, h->bvhSmemBytes, s>>>(h->ka); n++;
-        k_fire<<<h->gridFire, 128, h->bvhSmemBytes, s>>>(h->ka); n++;
+        if (h->cold) k_fire<true><<<h->gridFire, 128, h->bvhSmemBytes, s>>>(h->ka);
+        else k_fire<false><<<h->gridFire, 128, h->bvhSmemBytes, s>>>(h->ka);
+        n++;
     } else if (h->eventLog) {
         // pvpReplayLogic has no fireSystem: no fire events this step
         cudaMemsetAsync(h->ka.ctx.p.evAgent, 0,
                         (size_t)h->cfg.num_worlds * kAgents * kEventSlotsPerAgent * sizeof(GameEvent), s);
     }
-    k_world<<<h->gridWorld, 128, 0, s>>>(h->ka); n++;
+    if (h->cold) k_world<true><<<h->gridWorld, 128, 0, s>>>(h->ka);
+    else k_world<false><<<h->gridWorld, 128, 0, s>>>(h->ka);
+    n++;
     if (h->eventLog) {
         k_event_scan<<<1, 1024, 0, s>>>(h->ka, h->devEvOffset, h->devSnapOffset, h->devEvTotals); n++;
         k_event_scatter<<<h->gridSmall, 128, 0, s>>>(h->ka, h->devEvOffset, h->devSnapOffset, h->devEvOut,
@@ -365,6 +370,7 @@ int mpenv_create(const mpenv_config *cfg, mpenv_handle **out)
     h->eventLog = cfg->event_log_dir != nullptr;
     h->recordLog = cfg->record_log_path != nullptr;
     h->replayLog = cfg->replay_log_path != nullptr;
+    h->cold = h->eventLog || h->recordLog || h->replayLog || cfg->curriculum_data_path != nullptr;
     if (h->eventLog) h->eventDir = cfg->event_log_dir;
     if (h->recordLog) h->recordPath = cfg->record_log_path;
     if (h->replayLog) h->replayPath = cfg->replay_log_path;
@@ -512,15 +518,16 @@ int mpenv_create(const mpenv_config *cfg, mpenv_handle **out)
 
     if (h->bvhSmemBytes > 48 * 1024) {
         MP_CREATE(cudaFuncSetAttribute(k_move, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->bvhSmemBytes));
-        MP_CREATE(cudaFuncSetAttribute(k_fire, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->bvhSmemBytes));
+        MP_CREATE(cudaFuncSetAttribute(k_fire<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->bvhSmemBytes));
+        MP_CREATE(cudaFuncSetAttribute(k_fire<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->bvhSmemBytes));
         MP_CREATE(cudaFuncSetAttribute(k_los, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->bvhSmemBytes));
         MP_CREATE(cudaFuncSetAttribute(k_lidar, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->bvhSmemBytes));
     }
 
     const long long W = cfg->num_worlds, N = W * kAgents;
     h->gridMove = gridFor(h, k_move, 128, h->bvhSmemBytes, N);
-    h->gridFire = gridFor(h, k_fire, 128, h->bvhSmemBytes, N);
-    h->gridWorld = gridFor(h, k_world, 128, 0, W * 16);
+    h->gridFire = h->cold ? gridFor(h, k_fire<true>, 128, h->bvhSmemBytes, N) : gridFor(h, k_fire<false>, 128, h->bvhSmemBytes, N);
+    h->gridWorld = h->cold ? gridFor(h, k_world<true>, 128, 0, W * 16) : gridFor(h, k_world<false>, 128, 0, W * 16);
     h->gridLos = gridFor(h, k_los, 128, h->bvhSmemBytes, N * kTeamSize);
     h->gridObs = gridFor(h, k_obs, 128, 0, N * kObsRowsPerAgent);
     h->gridTeam = gridFor(h, k_fullteam, 128, 0, W * 2);
@@ -870,8 +877,8 @@ int mpenv_get_world_state(mpenv_handle *h, uint32_t world_idx, mpenv_world_state
 int mpenv_step_timed(mpenv_handle *h, float *kernel_ms, const char **kernel_names, uint32_t cap, uint32_t *count)
 {
     if (!h || !kernel_ms || !count) return MPENV_ERR_INVALID;
-    if (h->replayLog || h->eventLog || h->recordLog)
-        return fail(h, MPENV_ERR_INVALID, "mpenv_step_timed: not available with logs enabled");
+    if (h->cold)
+        return fail(h, MPENV_ERR_INVALID, "mpenv_step_timed: not available with logs / replay / curriculum enabled");
     MP_CUDA(h, cudaSetDevice(h->device));
     cudaStream_t s = h->stream;
     struct Item { const char *name; };
@@ -881,8 +888,8 @@ int mpenv_step_timed(mpenv_handle *h, float *kernel_ms, const char **kernel_name
     uint32_t n = 0;
     MP_CUDA(h, cudaEventRecord(ev[0], s));
     k_move<<<h->gridMove, 128, h->bvhSmemBytes, s>>>(h->ka); names[n++] = "k_move"; cudaEventRecord(ev[n], s);
-    k_fire<<<h->gridFire, 128, h->bvhSmemBytes, s>>>(h->ka); names[n++] = "k_fire"; cudaEventRecord(ev[n], s);
-    k_world<<<h->gridWorld, 128, 0, s>>>(h->ka); names[n++] = "k_world"; cudaEventRecord(ev[n], s);
+    k_fire<false><<<h->gridFire, 128, h->bvhSmemBytes, s>>>(h->ka); names[n++] = "k_fire"; cudaEventRecord(ev[n], s);
+    k_world<false><<<h->gridWorld, 128, 0, s>>>(h->ka); names[n++] = "k_world"; cudaEventRecord(ev[n], s);
     launchLos(h, s); names[n++] = "k_los"; cudaEventRecord(ev[n], s);
     k_obs<<<h->gridObs, 128, 0, s>>>(h->ka); names[n++] = "k_obs"; cudaEventRecord(ev[n], s);
     if (h->fullTeam) {

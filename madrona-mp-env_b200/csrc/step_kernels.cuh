@@ -87,6 +87,7 @@ __global__ void __launch_bounds__(128) k_move(KernelArgs ka)
         stageMove(c, i);
 }
 
+template <bool kCold>
 __global__ void __launch_bounds__(128) k_fire(KernelArgs ka)
 {
     extern __shared__ uint4 smem_raw[];
@@ -95,7 +96,7 @@ __global__ void __launch_bounds__(128) k_fire(KernelArgs ka)
     const int N = (int)c.cfg.numWorlds * kAgents;
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < N; i += gridDim.x * blockDim.x) {
         const int w = i / kAgents, a = i - w * kAgents;
-        stageFire(c, w, a, c.p.pos + (size_t)w * kAgents);
+        stageFire<kCold>(c, w, a, c.p.pos + (size_t)w * kAgents);
     }
 }
 
@@ -107,6 +108,7 @@ __global__ void __launch_bounds__(128) k_fire(KernelArgs ka)
 // graph order (sim.cpp:5508-5842).  __syncwarp() orders the phases' global-memory
 // traffic.  16x the threads of a thread-per-world launch: latency is what bounds
 // this stage.
+template <bool kCold>
 __global__ void __launch_bounds__(128) k_world(KernelArgs ka)
 {
     const Ctx &c = ka.ctx;
@@ -122,7 +124,7 @@ __global__ void __launch_bounds__(128) k_world(KernelArgs ka)
         const int base = w * kAgents;
         const bool agent = valid && lane < kAgents;
         const bool lead = valid && lane == 0;
-        if (c.cfg.replayLog) {
+        if (kCold && c.cfg.replayLog) {
             // pvpReplayLogic (sim.cpp:5587-5604): logged state, then the zone state machine
             if (lead) p.world[w].match.curStep = p.replayLog[w].curStep;
             if (agent) replayAgent(c, w, lane);
@@ -136,10 +138,10 @@ __global__ void __launch_bounds__(128) k_world(KernelArgs ka)
             if (agent) autoHealSystem(p, base + lane);
             __syncwarp();
             zoneSystemCoop(c, w, lane, half, valid);
-            if (c.cfg.recordLog && agent) recordAgent(c, w, lane);
+            if (kCold && c.cfg.recordLog && agent) recordAgent(c, w, lane);
             breadcrumbSystemsCoop(c, w, lane, half, valid);
         }
-        if (lead) zoneMatchInfoSystem(c, w);
+        if (lead) zoneMatchInfoSystem<kCold>(c, w);
         __syncwarp();
         evaluateGoalRegionsCoop(c, w, lane, half, valid);
         if (agent) {
@@ -158,7 +160,7 @@ __global__ void __launch_bounds__(128) k_world(KernelArgs ka)
                 p.ftReward[w * 2 + t] = r;
                 p.ftDone[w * 2 + t] = finished ? 1 : 0;
             }
-            resetSystem(c, w);
+            resetSystem<kCold>(c, w);
         }
         __syncwarp();
     }
