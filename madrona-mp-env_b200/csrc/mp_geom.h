@@ -409,15 +409,26 @@ MP_HD bool sphereCastNodeCheck(Vec3 o, Vec3 inv_d, float t_max, float sphere_r,
 // which ALWAYS tests two consecutive triangles whatever the leaf's triSize;
 // the vertex array is padded by one triangle so the last leaf's over-read is
 // defined).  Returns FLT_MAX on a miss; *out_n untouched on a miss.
+//
+// t_bound (default: none): the caller declares that it only distinguishes hits
+// with t < t_bound; anything at or beyond it is reported as a miss (FLT_MAX,
+// *out_n untouched).  Hits below the bound are bit-identical to the unbounded
+// cast: a triangle's contact time does not depend on the running bound (the
+// bound only rejects candidates >= it, in every stage of sphereCastTriangle --
+// including its plane_t >= t_max early-out, since no feature of a triangle is
+// touched before its plane), first-wins tie order is unchanged, and a culled
+// node's expanded box is entered at t >= t_bound.  The reference sweeps to
+// infinity (mesh_bvh.inl:760) and the step then clamps the result to the
+// distance moved this tick; bounding the sweep skips the far side of the map.
 MP_HD_NOINLINE float bvhSphereCast(const BVHView &bvh, Vec3 ray_o, Vec3 ray_d, float sphere_r,
-                                   Vec3 *out_n)
+                                   Vec3 *out_n, float t_bound = FLT_MAX)
 {
     Vec3 inv_d = v3(1.f / ray_d.x, 1.f / ray_d.y, 1.f / ray_d.z);
     int32_t stack[32];
     int32_t stack_size = 0;
     stack[stack_size++] = 0;
     Vec3 closest_n = v3(0.f, 0.f, 0.f);
-    const float t_max = FLT_MAX;
+    const float t_max = t_bound;
     float hit_t = t_max;
     while (stack_size > 0) {
         const BVHNode &node = bvh.nodes[stack[--stack_size]];
@@ -450,7 +461,7 @@ MP_HD_NOINLINE float bvhSphereCast(const BVHView &bvh, Vec3 ray_o, Vec3 ray_d, f
         }
     }
     if (hit_t < t_max) *out_n = closest_n;
-    return hit_t;
+    return hit_t < t_max ? hit_t : FLT_MAX;
 }
 
 }  // namespace mpenv

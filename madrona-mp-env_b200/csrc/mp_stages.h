@@ -169,15 +169,18 @@ MP_HD void applyVelocitySystem(const BVHView &bvh, Vec3 pos, Vec3 vel, int32_t c
     bvhSphereCast(bvh, ray_o, -kUp(), r, &normal);
     if (normal.z > 0.0f && (double)normal.z < 0.7 && dot(normal, v_norm) < 0.0f) return;
 
+    // Everything below uses the forward casts only through fmaxf(0, t - buffer) compared
+    // with / clamped to move_dist (and t == 0), so hits past move_dist + buffer are misses.
+    const float fwd_bound = (move_dist + buffer) * 1.001f + 0.01f;
     ray_o = x + v_norm * buffer * 0.5f;
     ray_o.z += low_check_height;
-    float low_dist = bvhSphereCast(bvh, ray_o, v_norm, r, &normal);
+    float low_dist = bvhSphereCast(bvh, ray_o, v_norm, r, &normal, fwd_bound);
     float high_dist = low_dist;
     bool high_hit = false;
     if (cur_pose != 2) {
         ray_o.z = x.z + top_of_capsule;
         Vec3 high_normal = v3(0, 0, 0);
-        high_dist = bvhSphereCast(bvh, ray_o, v_norm, r, &high_normal);
+        high_dist = bvhSphereCast(bvh, ray_o, v_norm, r, &high_normal, fwd_bound);
         if (high_dist < low_dist) {
             low_dist = high_dist;
             normal = high_normal;
@@ -195,9 +198,10 @@ MP_HD void applyVelocitySystem(const BVHView &bvh, Vec3 pos, Vec3 vel, int32_t c
         ray_o = x + v_norm * low_dist;
         ray_o.z += high_hit ? top_of_capsule : low_check_height;
         Vec3 tmp_n;
-        float slide_dist = bvhSphereCast(bvh, ray_o, slide_dir, r, &tmp_n);
-        slide_dist = fmaxf(0.0f, slide_dist - buffer);
         float max_move = move_dist - low_dist;
+        // clamped to max_move below: same argument
+        float slide_dist = bvhSphereCast(bvh, ray_o, slide_dir, r, &tmp_n, (max_move + buffer) * 1.001f + 0.01f);
+        slide_dist = fmaxf(0.0f, slide_dist - buffer);
         slide_dist = fminf(slide_dist, max_move);
         if (slide_dist > 0.0f) hit_pos = hit_pos + slide_dir * slide_dist;
     }
