@@ -80,6 +80,8 @@ typedef struct mpenv_config {
      * of a steps.bin record after its 16-byte header).  Half of the non-eval episodes then
      * start from a random snapshot (level_gen.cpp:498-581).  NULL = off. */
     const char *curriculum_data_path;
+    uint32_t train_flank;        /* Config::trainFlank (mgr.hpp:46): RewardMode::Flank, flankRewardSystem
+                                    (sim.cpp:4211-4290) instead of zoneRewardSystem */
 } mpenv_config;
 
 typedef struct mpenv_handle mpenv_handle;

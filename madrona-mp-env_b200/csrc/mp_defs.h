@@ -323,6 +323,7 @@ struct SimConfig {
     int32_t recordLog;                  // TaskConfig::recordLog != nullptr
     int32_t replayLog;                  // TaskConfig::replayLog != nullptr
     int32_t numCurriculumSnapshots;     // TrajectoryCurriculum::numSnapshots (mgr.cpp:1419-1441)
+    int32_t rewardFlank;                // TaskConfig::rewardMode == RewardMode::Flank (mgr.cpp:1745-1750)
 };
 
 // TrainControl (types.hpp:158), live tensor (mgr.cpp:287-293)

@@ -298,5 +298,5 @@ MP_HD void stageMove(const Ctx &c, int idx)
 
 }  // namespace mpenv
 
-#include "mp_stages_world.h"
 #include "mp_stages_obs.h"
+#include "mp_stages_world.h"

@@ -40,6 +40,21 @@ MP_HD Vec3 losSamplePoint(Vec3 base_pos, float view_h, Vec3 delta_right, int s)
     return pt;
 }
 
+// isAgentVisible (utils.cpp:186-271): any of the four sample points of agent `target`
+// (index in world) seen from `o` looking along `aim`.
+MP_HD bool agentVisible(const Ctx &c, int w, const Vec3 *world_pos, Vec3 o, const Aim &aim, int target)
+{
+    const Quat inv = quatInv(aim.rot);
+    const float view_h = viewHeight(c.p.stand[w * kAgents + target].cur);
+    const Vec3 delta_right = rotateVec(aim.rot, kRight()) * 0.9f * kAgentRadius;
+    bool any = false;
+    for (int s = 0; s < 4; s++) {      // bottom, top, left, right (utils.cpp:253-267)
+        const Vec3 pt = losSamplePoint(world_pos[target], view_h, delta_right, s);
+        if (losSampleVisible(c, world_pos, o, inv, pt, target)) any = true;
+    }
+    return any;
+}
+
 // opponentsWriteVisibilitySystem (sim.cpp:2526-2560) for one (agent, opponent
 // slot) pair.  Returns canSee.
 MP_HD bool visibilityPair(const Ctx &c, int w, int a, int j, const Vec3 *world_pos)

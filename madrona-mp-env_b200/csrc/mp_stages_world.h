@@ -695,6 +695,50 @@ MP_HD void exploreVisitedSystem(const Ctx &c, int w, int idx)
     }
 }
 
+// flankRewardSystem (sim.cpp:4211-4290): RewardMode::Flank (Manager::Config::trainFlank)
+// replaces zoneRewardSystem in the Step graph (sim.cpp:5733-5748).  Note the reference
+// tests "can the opponent see me" along the AGENT's own aim (sim.cpp:4261).
+MP_HD void flankRewardSystem(const Ctx &c, int w, int a)
+{
+    const SimPtrs &p = c.p;
+    const int base = w * kAgents;
+    const int idx = base + a;
+    const Vec3 *world_pos = p.pos + base;
+    const Vec3 pos = p.pos[idx];
+    const Aim aim = p.aim[idx];
+    float reward = 0.f;
+    Vec3 vis_check_pos = pos;
+    vis_check_pos.z += viewHeight(p.stand[idx].cur);
+    constexpr float flank_dist = 100.f;
+    const int team = teamOf(a);
+    float teammate_reward = 0.f;
+    for (int i = 0; i < kTeamSize; i++) {
+        const int mate = team * kTeamSize + i;
+        if (mate == a) continue;
+        const Vec3 dir = world_pos[mate] - pos;
+        const bool visible = agentVisible(c, w, world_pos, vis_check_pos, aim, mate);
+        if (length2(dir) >= flank_dist * flank_dist || !visible) teammate_reward += 0.001f;
+    }
+    reward += teammate_reward;
+    float opponent_reward = 0.f;
+    for (int i = 0; i < kTeamSize; i++) {
+        const int opp = (team ^ 1) * kTeamSize + i;
+        Vec3 opp_pos = world_pos[opp];
+        opp_pos.z += viewHeight(p.stand[base + opp].cur);
+        if (!agentVisible(c, w, world_pos, opp_pos, aim, a)) opponent_reward += 0.001f;
+    }
+    reward += opponent_reward;
+    const CombatState &cs = p.combat[idx];
+    if (cs.landedShotOn >= 0) {
+        const float yaw_diff = fabsf(p.aim[base + cs.landedShotOn].yaw - aim.yaw);
+        if (yaw_diff > kPi) reward += cs.successfulKill ? 1.f : 0.2f;
+    }
+    const uint32_t num_new_cells = p.exploreNew[idx];
+    p.exploreNew[idx] = 0;
+    if (num_new_cells > 0) reward += float(num_new_cells) * p.rewardCoefs[idx].exploreScale;
+    p.reward[idx] = reward;
+}
+
 // zoneRewardSystem (sim.cpp:3849-3996) incl. learnShootingRewardSystem
 // (:3707-3732) under the LearnShooting world curriculum.
 MP_HD void zoneRewardSystem(const Ctx &c, int w, int a)
@@ -1065,7 +1109,10 @@ MP_HD void stageWorld(const Ctx &c, int w)
     zoneMatchInfoSystem(c, w);
     evaluateGoalRegionsSystem(c, w);
     for (int i = 0; i < kAgents; i++) exploreVisitedSystem(c, w, base + i);
-    for (int i = 0; i < kAgents; i++) zoneRewardSystem(c, w, i);
+    for (int i = 0; i < kAgents; i++) {
+        if (c.cfg.rewardFlank) flankRewardSystem(c, w, i);
+        else zoneRewardSystem(c, w, i);
+    }
     teamAndFinalReward(c, w);
     const int32_t finished = p.world[w].match.isFinished;
     for (int i = 0; i < kAgents; i++) p.done[base + i] = finished;

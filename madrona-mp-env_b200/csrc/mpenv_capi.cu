@@ -370,7 +370,8 @@ int mpenv_create(const mpenv_config *cfg, mpenv_handle **out)
     h->eventLog = cfg->event_log_dir != nullptr;
     h->recordLog = cfg->record_log_path != nullptr;
     h->replayLog = cfg->replay_log_path != nullptr;
-    h->cold = h->eventLog || h->recordLog || h->replayLog || cfg->curriculum_data_path != nullptr;
+    h->cold = h->eventLog || h->recordLog || h->replayLog || cfg->curriculum_data_path != nullptr ||
+              cfg->train_flank != 0;
     if (h->eventLog) h->eventDir = cfg->event_log_dir;
     if (h->recordLog) h->recordPath = cfg->record_log_path;
     if (h->replayLog) h->replayPath = cfg->replay_log_path;
@@ -433,6 +434,7 @@ int mpenv_create(const mpenv_config *cfg, mpenv_handle **out)
     ka.ctx.cfg.eventLog = h->eventLog ? 1 : 0;
     ka.ctx.cfg.recordLog = h->recordLog ? 1 : 0;
     ka.ctx.cfg.replayLog = h->replayLog ? 1 : 0;
+    ka.ctx.cfg.rewardFlank = cfg->train_flank ? 1 : 0;
 
     // navmesh + A* table for the scripted bot (LevelData, sim.cpp:5895-5898)
     if (h->assets.hasNav) {

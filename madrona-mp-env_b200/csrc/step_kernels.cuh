@@ -146,7 +146,8 @@ __global__ void __launch_bounds__(128) k_world(KernelArgs ka)
         evaluateGoalRegionsCoop(c, w, lane, half, valid);
         if (agent) {
             exploreVisitedSystem(c, w, base + lane);
-            zoneRewardSystem(c, w, lane);
+            if (kCold && c.cfg.rewardFlank) flankRewardSystem(c, w, lane);
+            else zoneRewardSystem(c, w, lane);
         }
         __syncwarp();
         if (lead) {

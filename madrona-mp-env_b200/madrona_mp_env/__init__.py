@@ -53,7 +53,8 @@ class _Config(C.Structure):
                 ("policy_history_size", C.c_uint32), ("scene_dir", C.c_char_p),
                 ("world_id_offset", C.c_uint32), ("enable_full_team", C.c_uint32),
                 ("event_log_dir", C.c_char_p), ("record_log_path", C.c_char_p),
-                ("replay_log_path", C.c_char_p), ("curriculum_data_path", C.c_char_p)]
+                ("replay_log_path", C.c_char_p), ("curriculum_data_path", C.c_char_p),
+                ("train_flank", C.c_uint32)]
 
 
 class _TensorDesc(C.Structure):
@@ -138,8 +139,6 @@ class SimManager:
                  curriculum_data_path=None, world_id_offset=0, enable_full_team=True):
         if int(exec_mode) != int(ExecMode.CUDA):
             raise ValueError("madrona_mp_env (B200): only ExecMode.CUDA exists; there is no CPU path")
-        if train_flank:
-            raise NotImplementedError("train_flank (RewardMode::Flank) is outside this build's scope")
         self._lib = _load()
         self._scene = os.fsencode(scene_path)
         # mgr.hpp:47-49; the C ABI copies the strings
@@ -148,7 +147,7 @@ class SimManager:
                       int(sim_flags), int(task_type), int(team_size), int(num_pbt_policies),
                       int(policy_history_size), self._scene, int(world_id_offset), int(enable_full_team),
                       enc(event_log_path), enc(record_log_path), enc(replay_log_path),
-                      enc(curriculum_data_path))
+                      enc(curriculum_data_path), int(bool(train_flank)))
         self._h = C.c_void_p()
         rc = self._lib.mpenv_create(C.byref(cfg), C.byref(self._h))
         if rc != 0:

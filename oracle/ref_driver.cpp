@@ -72,6 +72,7 @@ struct RefConfig {
     const uint32_t *navTriIndices;        // numNavTris x 3
     const int32_t *navTriAdjacency;       // numNavTris x 3
     const uint32_t *navLookup;            // numNavTris x numNavTris
+    uint32_t trainFlank;                  // Config::trainFlank -> RewardMode::Flank (mgr.cpp:1745-1750)
 };
 
 struct RefSim {
@@ -357,7 +358,7 @@ void * ref_create(const RefConfig *cfg, const char *scene_dir,
     tc.spawnCurriculum = s->spawnCurriculum;
     tc.zones = zones;
     tc.task = Task(cfg->taskType);
-    tc.rewardMode = RewardMode::Default;
+    tc.rewardMode = cfg->trainFlank ? RewardMode::Flank : RewardMode::Default;
     tc.highlevelMove = false;
     tc.viz = nullptr;
     if (cfg->enableRecordLog) s->recordLog.resize(cfg->numWorlds);

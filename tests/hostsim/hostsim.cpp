@@ -65,6 +65,7 @@ struct HostSimConfig {
     uint32_t enableEventLog, enableRecordLog, enableReplayLog;
     uint32_t numCurriculumSnapshots;
     const void *curriculumSnapshots;
+    uint32_t trainFlank;
 };
 
 void *hostsim_create(const HostSimConfig *cfg, const char *scene_dir)
@@ -88,6 +89,7 @@ void *hostsim_create(const HostSimConfig *cfg, const char *scene_dir)
     c.cfg.eventLog = cfg->enableEventLog ? 1 : 0;
     c.cfg.recordLog = cfg->enableRecordLog ? 1 : 0;
     c.cfg.replayLog = cfg->enableReplayLog ? 1 : 0;
+    c.cfg.rewardFlank = cfg->trainFlank ? 1 : 0;
     c.mc = &s->consts;
     c.bvh.nodes = s->assets.nodes.data();
     c.bvh.verts = s->assets.verts.data();

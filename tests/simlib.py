@@ -291,7 +291,7 @@ class RefConfig(C.Structure):
                 ("enableReplayLog", C.c_uint32), ("numCurriculumSnapshots", C.c_uint32),
                 ("curriculumSnapshots", C.c_void_p), ("numNavVerts", C.c_uint32), ("numNavTris", C.c_uint32),
                 ("navVerts", C.c_void_p), ("navTriIndices", C.c_void_p), ("navTriAdjacency", C.c_void_p),
-                ("navLookup", C.c_void_p)]
+                ("navLookup", C.c_void_p), ("trainFlank", C.c_uint32)]
 
 
 # Log record layouts (reference types.hpp:574-634, 729-760; csrc/mp_defs.h).
@@ -381,7 +381,7 @@ class Oracle(_SimBase):
 
     def __init__(self, num_worlds, rand_seed=10, auto_reset=False, sim_flags=0, det=True,
                  world_id_offset=0, num_threads=1, scene=SCENE, bvh=None, event_log=False,
-                 record_log=False, replay_log=False, curriculum=None, navmesh=True):
+                 record_log=False, replay_log=False, curriculum=None, navmesh=True, train_flank=False):
         build_oracle()
         self.lib = C.CDLL(REF_DET_SO if det else REF_SO)
         L = self.lib
@@ -411,6 +411,7 @@ class Oracle(_SimBase):
                         world_id_offset, num_threads, int(event_log), int(record_log), int(replay_log),
                         0 if curriculum is None else len(curriculum),
                         None if curriculum is None else np.ascontiguousarray(curriculum).ctypes.data)
+        cfg.trainFlank = int(train_flank)
         if navmesh:
             nv, nt, na, nl = self._nav = load_navmesh(C.CDLL(build_hostsim()), scene)
             cfg.numNavVerts, cfg.numNavTris = len(nv), len(nt)
@@ -512,7 +513,7 @@ class HostSimConfig(C.Structure):
                 ("simFlags", C.c_uint32), ("worldIDOffset", C.c_uint32), ("enableFullTeam", C.c_uint32),
                 ("enableEventLog", C.c_uint32), ("enableRecordLog", C.c_uint32),
                 ("enableReplayLog", C.c_uint32), ("numCurriculumSnapshots", C.c_uint32),
-                ("curriculumSnapshots", C.c_void_p)]
+                ("curriculumSnapshots", C.c_void_p), ("trainFlank", C.c_uint32)]
 
 
 class HostSim(_SimBase):
@@ -520,7 +521,7 @@ class HostSim(_SimBase):
 
     def __init__(self, num_worlds, rand_seed=10, auto_reset=False, sim_flags=0, world_id_offset=0,
                  full_team=True, scene=SCENE, event_log=False, record_log=False, replay_log=False,
-                 curriculum=None):
+                 curriculum=None, train_flank=False):
         self.lib = C.CDLL(build_hostsim())
         L = self.lib
         L.hostsim_create.restype = C.c_void_p
@@ -536,7 +537,8 @@ class HostSim(_SimBase):
         cfg = HostSimConfig(num_worlds, rand_seed, int(auto_reset), sim_flags, world_id_offset,
                             int(full_team), int(event_log), int(record_log), int(replay_log),
                             0 if curriculum is None else len(curriculum),
-                            None if curriculum is None else np.ascontiguousarray(curriculum).ctypes.data)
+                            None if curriculum is None else np.ascontiguousarray(curriculum).ctypes.data,
+                            int(train_flank))
         L.hostsim_read_event_log.restype = C.c_int64
         L.hostsim_read_event_log.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint64]
         L.hostsim_record_log.restype = C.c_void_p
@@ -699,7 +701,8 @@ class MpenvConfig(C.Structure):
                 ("policy_history_size", C.c_uint32), ("scene_dir", C.c_char_p),
                 ("world_id_offset", C.c_uint32), ("enable_full_team", C.c_uint32),
                 ("event_log_dir", C.c_char_p), ("record_log_path", C.c_char_p),
-                ("replay_log_path", C.c_char_p), ("curriculum_data_path", C.c_char_p)]
+                ("replay_log_path", C.c_char_p), ("curriculum_data_path", C.c_char_p),
+                ("train_flank", C.c_uint32)]
 
 
 class TensorDesc(C.Structure):
@@ -740,7 +743,7 @@ class GpuSim(_SimBase):
 
     def __init__(self, num_worlds, rand_seed=10, auto_reset=False, sim_flags=0, world_id_offset=0,
                  full_team=True, scene=SCENE, gpu_id=0, event_log=False, record_log=False, replay_log=False,
-                 curriculum_path=None):
+                 curriculum_path=None, train_flank=False):
         """event_log / record_log / replay_log: False = off, True = in memory only,
         a path = the reference's files (event_log: directory)."""
         self.lib = load_product()
@@ -749,7 +752,7 @@ class GpuSim(_SimBase):
         self._log_paths = [path(event_log), path(record_log), path(replay_log),
                            None if curriculum_path is None else str(curriculum_path).encode()]
         cfg = MpenvConfig(gpu_id, num_worlds, rand_seed, int(auto_reset), sim_flags, 2, 6, 0, 1,
-                          self._scene, world_id_offset, int(full_team), *self._log_paths)
+                          self._scene, world_id_offset, int(full_team), *self._log_paths, int(train_flank))
         self.h = C.c_void_p()
         rc = self.lib.mpenv_create(C.byref(cfg), C.byref(self.h))
         if rc != 0:

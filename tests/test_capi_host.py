@@ -84,10 +84,10 @@ def test_create_argument_errors(lib):
     h = C.c_void_p()
     scene = S.SCENE.encode()
     bad = [
-        S.MpenvConfig(0, 4, 10, 0, 0, 1, 6, 0, 1, scene, 0, 1, None, None, None, None),            # TDM: unsupported task
-        S.MpenvConfig(0, 4, 10, 0, 0, 2, 4, 0, 1, scene, 0, 1, None, None, None, None),            # team size
-        S.MpenvConfig(0, 0, 10, 0, 0, 2, 6, 0, 1, scene, 0, 1, None, None, None, None),            # zero worlds
-        S.MpenvConfig(0, 4, 10, 0, 1 << 11, 2, 6, 0, 1, scene, 0, 1, None, None, None, None),      # SubZones flag
+        S.MpenvConfig(0, 4, 10, 0, 0, 1, 6, 0, 1, scene, 0, 1, None, None, None, None, 0),            # TDM: unsupported task
+        S.MpenvConfig(0, 4, 10, 0, 0, 2, 4, 0, 1, scene, 0, 1, None, None, None, None, 0),            # team size
+        S.MpenvConfig(0, 0, 10, 0, 0, 2, 6, 0, 1, scene, 0, 1, None, None, None, None, 0),            # zero worlds
+        S.MpenvConfig(0, 4, 10, 0, 1 << 11, 2, 6, 0, 1, scene, 0, 1, None, None, None, None, 0),      # SubZones flag
     ]
     for cfg in bad:
         assert lib.mpenv_create(C.byref(cfg), C.byref(h)) == -1           # MPENV_ERR_INVALID
@@ -106,7 +106,7 @@ def _have_cuda():
 def test_no_cuda_fails_loudly(lib):
     """There is no CPU execution path: without a device create() must fail."""
     h = C.c_void_p()
-    cfg = S.MpenvConfig(0, 4, 10, 0, 0, 2, 6, 0, 1, S.SCENE.encode(), 0, 1, None, None, None, None)
+    cfg = S.MpenvConfig(0, 4, 10, 0, 0, 2, 6, 0, 1, S.SCENE.encode(), 0, 1, None, None, None, None, 0)
     assert lib.mpenv_create(C.byref(cfg), C.byref(h)) == -3               # MPENV_ERR_CUDA
     assert b"no usable CUDA device" in lib.mpenv_last_error(None)
     import madrona_mp_env as mp

@@ -155,3 +155,26 @@ def test_trajectory_curriculum_gpu(tmp_path, built):
                     assert not dd, f"flags {flags} step {s} world {w}: {dd[:6]}"
         finally:
             gpu.close(); orc.close()
+
+
+def test_flank_reward_mode_gpu():
+    """train_flank (bindings.cpp:104, mgr.cpp:1745-1750): flankRewardSystem on the device."""
+    W = 8
+    gpu = S.GpuSim(W, auto_reset=True, train_flank=True)
+    orc = S.Oracle(W, auto_reset=True, det=True, train_flank=True)
+    try:
+        gpu.init(); orc.init()
+        for s in range(200):
+            d, a = S.seek_policy(orc, s, W)
+            for sim in (gpu, orc):
+                sim.set_actions(d, a)
+                sim.step()
+            for name in S.STEP_OUTPUTS:
+                x, y = gpu.export(name), orc.export(name)
+                assert np.array_equal(x.view(np.int32), y.view(np.int32)), f"step {s}: {name}"
+        for w in range(W):
+            dd = S.diff_world_state(gpu.world_state(w), orc.world_state(w))
+            assert not dd, f"world {w}: {dd[:6]}"
+        assert np.abs(orc.export("reward")).sum() > 0
+    finally:
+        gpu.close(); orc.close()

@@ -176,3 +176,32 @@ def test_trajectory_curriculum_matches_oracle(built):
         finally:
             host.close(); orc.close()
     assert restored > 0, "no world started from a snapshot"
+
+
+def test_flank_reward_mode_matches_oracle(built):
+    """Manager::Config::trainFlank -> RewardMode::Flank: flankRewardSystem (sim.cpp:4211-4290)
+    replaces zoneRewardSystem; 11 more isAgentVisible checks per agent."""
+    W = 4
+    host = S.HostSim(W, auto_reset=True, train_flank=True)
+    orc = S.Oracle(W, auto_reset=True, det=True, train_flank=True)
+    plain = S.Oracle(W, auto_reset=True, det=True)
+    differs = False
+    try:
+        for sim in (host, orc, plain):
+            sim.init()
+        for s in range(200):
+            d, a = S.seek_policy(orc, s, W)
+            for sim in (host, orc, plain):
+                sim.set_actions(d, a)
+                sim.step()
+            for name in S.STEP_OUTPUTS:
+                x, y = host.export(name), orc.export(name)
+                assert np.array_equal(x.view(np.int32), y.view(np.int32)), f"step {s}: {name}"
+            if s % 20 == 19:
+                for w in range(W):
+                    dd = S.diff_world_state(host.world_state(w), orc.world_state(w))
+                    assert not dd, f"step {s} world {w}: {dd[:6]}"
+            differs |= not np.array_equal(orc.export("reward"), plain.export("reward"))
+        assert differs, "flank rewards never differed from the default reward mode"
+    finally:
+        host.close(); orc.close(); plain.close()
