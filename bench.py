@@ -226,6 +226,13 @@ def run_ours(args):
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         cpu_baseline = run_cpu_sample(S, cores=0)
 
+    census = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        try:
+            census = ray_census(S, local)
+        except Exception as exc:           # the census is a side measurement: never fail the bench line
+            census = {"unavailable": str(exc)[:200]}
+
     if rank == 0:
         line = {
             "metric": METRIC, "value": round(value, 1), "unit": "agent-steps/s", "n_gpus": world,
@@ -239,11 +246,36 @@ def run_ours(args):
             "clocks": sampler.summary() if rank == 0 else None,
             "e2e": e2e, "gpu_launches": mgr_launches(lib, h) * args.steps,
             "roofline": roofline, "cpu_baseline": cpu_baseline,
-            "rays_per_s_estimate": round(value * 105, 1),
+            "rays_per_agent_step": census,
+            "bvh_rays_per_s": (round(value * census["rays"], 1) if census and "rays" in census
+                               else None),
+            "sphere_casts_per_s": (round(value * census["sphere_casts"], 1) if census and "rays" in census
+                                   else None),
         }
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
+
+
+def ray_census(S, gpu_id, worlds=2048, warmup=60, steps=40):
+    """Rays per agent-step from the INSTRUMENTED twin library (device counters where the
+    reference calls traceRayAgainstWorld / sphereCast), on the same workload at a
+    smaller batch.  Never timed: the rate is this count x the timed agent-steps/s."""
+    sim = S.GpuSim(worlds, auto_reset=True, full_team=False, gpu_id=gpu_id, instrumented=True)
+    try:
+        sim.init()
+        for s in range(warmup + steps):
+            if s == warmup:
+                sim.ray_counts(reset=True)
+            d, a = S.random_actions(s, worlds)
+            sim.set_actions(d, a)
+            sim.step()
+        c = sim.ray_counts().astype(float) / (worlds * AGENTS * steps)
+    finally:
+        sim.close()
+    return {"lidar": round(c[0], 3), "line_of_sight": round(c[1], 3), "hitscan": round(c[2], 3),
+            "sphere_casts": round(c[3], 3), "rays": round(c[0] + c[1] + c[2], 3),
+            "sample": f"{worlds} worlds x {steps} steps after {warmup} warm-up, libmpenv_b200_count.so"}
 
 
 def mgr_launches(lib, h):

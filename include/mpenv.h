@@ -215,6 +215,13 @@ int mpenv_get_world_state(mpenv_handle *h, uint32_t world_idx, mpenv_world_state
 /* Number of kernel launches issued by one step / one init (for bench accounting). */
 int mpenv_launches_per_step(mpenv_handle *h, uint32_t *step_launches, uint32_t *init_launches);
 
+/* Ray census of the INSTRUMENTED build (libmpenv_b200_count.so = same sources with
+ * -DMPENV_COUNT_RAYS): cumulative counts since the last reset of
+ * out[0] lidar rays, out[1] line-of-sight rays, out[2] hitscan rays, out[3] swept-sphere
+ * casts, counted where the reference calls traceRayAgainstWorld / sphereCast.  The product
+ * library returns MPENV_ERR_INVALID (its kernels carry no counters). */
+int mpenv_ray_counts(mpenv_handle *h, uint64_t *out, int32_t reset);
+
 /* Measurement aid: runs ONE step as individual launches on the handle's stream
  * with a CUDA event pair around each kernel; writes up to `cap` durations (ms)
  * and the matching kernel names.  Synchronous.  Same kernels and results as

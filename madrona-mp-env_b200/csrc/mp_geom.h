@@ -15,6 +15,22 @@
 
 namespace mpenv {
 
+// Ray census ("BVH rays/s ... counted with a device counter in an
+// instrumented build, not in the timed build"): libmpenv_b200_count.so is the same
+// source compiled with -DMPENV_COUNT_RAYS; the product library compiles these away.
+// [0] lidar rays, [1] line-of-sight rays, [2] hitscan rays, [3] swept-sphere casts --
+// counted where the reference would call traceRayAgainstWorld / sphereCast.
+#if defined(MPENV_COUNT_RAYS) && defined(__CUDACC__)
+__device__ unsigned long long g_rayCounts[4];
+#if defined(__CUDA_ARCH__)
+#define MP_COUNT_RAYS(kind, n) atomicAdd(&g_rayCounts[kind], (unsigned long long)(n))
+#else
+#define MP_COUNT_RAYS(kind, n) ((void)0)
+#endif
+#else
+#define MP_COUNT_RAYS(kind, n) ((void)0)
+#endif
+
 // ---------------------------------------------------------------- ray / tri
 // Woop et al. watertight ray/triangle setup (reference mesh_bvh.inl:584-741;
 // only the shear constants are consumed by the triangle test).
@@ -423,6 +439,7 @@ MP_HD bool sphereCastNodeCheck(Vec3 o, Vec3 inv_d, float t_max, float sphere_r,
 MP_HD_NOINLINE float bvhSphereCast(const BVHView &bvh, Vec3 ray_o, Vec3 ray_d, float sphere_r,
                                    Vec3 *out_n, float t_bound = FLT_MAX)
 {
+    MP_COUNT_RAYS(3, 1);
     Vec3 inv_d = v3(1.f / ray_d.x, 1.f / ray_d.y, 1.f / ray_d.z);
     int32_t stack[32];
     int32_t stack_size = 0;

@@ -104,6 +104,7 @@ MP_HD void stageFire(const Ctx &c, int w, int a, const Vec3 *world_pos)
     Vec3 fire_dir = rotateVec(aim.rot, kFwd());
     float hit_t;
     int32_t hit_agent;
+    MP_COUNT_RAYS(2, 1);
     bool hit = traceRayWorld(c.bvh, world_pos, fire_from, fire_dir, &hit_t, &hit_agent);
     cs.firedShotT = hit ? hit_t : FLT_MAX;
 

@@ -909,6 +909,26 @@ int mpenv_step_timed(mpenv_handle *h, float *kernel_ms, const char **kernel_name
     return MPENV_OK;
 }
 
+int mpenv_ray_counts(mpenv_handle *h, uint64_t *out, int32_t reset)
+{
+    if (!h || !out) return MPENV_ERR_INVALID;
+#if defined(MPENV_COUNT_RAYS)
+    MP_CUDA(h, cudaSetDevice(h->device));
+    MP_CUDA(h, cudaStreamSynchronize(h->stream));
+    unsigned long long host[4];
+    MP_CUDA(h, cudaMemcpyFromSymbol(host, g_rayCounts, sizeof(host)));
+    for (int i = 0; i < 4; i++) out[i] = host[i];
+    if (reset) {
+        unsigned long long zero[4] = { 0, 0, 0, 0 };
+        MP_CUDA(h, cudaMemcpyToSymbol(g_rayCounts, zero, sizeof(zero)));
+    }
+    return MPENV_OK;
+#else
+    (void)reset;
+    return fail(h, MPENV_ERR_INVALID, "mpenv_ray_counts: not an instrumented build (use libmpenv_b200_count.so)");
+#endif
+}
+
 int mpenv_launches_per_step(mpenv_handle *h, uint32_t *step_launches, uint32_t *init_launches)
 {
     if (!h) return MPENV_ERR_INVALID;

@@ -108,6 +108,7 @@ __global__ void __launch_bounds__(kLidarWarpsPerCTA * 32, 3) k_lidar_pool(Kernel
         }
         __syncwarp();
 
+        if (lane == 0) MP_COUNT_RAYS(0, kLidarTaskRays);
         // ---- phase 2: closest mesh hit of the 160 rays
         LidarPoolAccess acc{&P};
         traversePool<kBatch, kRefill>(bvh, acc);
@@ -248,6 +249,12 @@ __global__ void __launch_bounds__(kLosWarpsPerCTA * 32, 2) k_los_pool(KernelArgs
                     ok = ok && !(len < kAgentRadius);
                     dir = to_test / len;
                 }
+#if defined(MPENV_COUNT_RAYS)
+                {   // the reference traces every candidate that survives the view-space cull
+                    const unsigned cm = __ballot_sync(0xFFFFFFFFu, ok);
+                    if (lane == 0 && cm) MP_COUNT_RAYS(1, __popc(cm));
+                }
+#endif
                 // The agent capsules first (utils.cpp:39-61): the sample sees its target only
                 // if, among the capsules, the target is the one traceRayAgainstWorld would
                 // pick -- earlier agents must be strictly farther, later ones not nearer --

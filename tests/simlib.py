@@ -710,11 +710,17 @@ class TensorDesc(C.Structure):
                 ("dims", C.c_int64 * 4), ("gpu_id", C.c_int32)]
 
 
-def load_product():
-    """Loads libmpenv_b200.so (built by __graft_entry__.build()); no fallback."""
-    if not os.path.exists(PRODUCT_SO):
-        raise RuntimeError(f"{PRODUCT_SO} is missing: run `python -c 'import __graft_entry__ as g; g.build()'`")
-    L = C.CDLL(PRODUCT_SO)
+COUNT_SO = os.path.join(os.path.dirname(PRODUCT_SO), "libmpenv_b200_count.so")
+
+
+def load_product(so=None):
+    """Loads libmpenv_b200.so (built by __graft_entry__.build()); no fallback.
+    so=COUNT_SO: the instrumented twin (ray census, never timed)."""
+    so = so or PRODUCT_SO
+    if not os.path.exists(so):
+        raise RuntimeError(f"{so} is missing: run `python -c 'import __graft_entry__ as g; g.build()'`")
+    L = C.CDLL(so)
+    L.mpenv_ray_counts.argtypes = [C.c_void_p, C.c_void_p, C.c_int32]
     L.mpenv_create.argtypes = [C.POINTER(MpenvConfig), C.POINTER(C.c_void_p)]
     for f in ("mpenv_destroy", "mpenv_init", "mpenv_step", "mpenv_sync"):
         getattr(L, f).argtypes = [C.c_void_p]
@@ -743,10 +749,11 @@ class GpuSim(_SimBase):
 
     def __init__(self, num_worlds, rand_seed=10, auto_reset=False, sim_flags=0, world_id_offset=0,
                  full_team=True, scene=SCENE, gpu_id=0, event_log=False, record_log=False, replay_log=False,
-                 curriculum_path=None, train_flank=False):
-        """event_log / record_log / replay_log: False = off, True = in memory only,
+                 curriculum_path=None, train_flank=False, instrumented=False):
+        """instrumented: load libmpenv_b200_count.so (mpenv_ray_counts works there).
+        event_log / record_log / replay_log: False = off, True = in memory only,
         a path = the reference's files (event_log: directory)."""
-        self.lib = load_product()
+        self.lib = load_product(COUNT_SO if instrumented else None)
         self._scene = scene.encode()
         path = lambda v: None if v is False or v is None else (b"" if v is True else str(v).encode())
         self._log_paths = [path(event_log), path(record_log), path(replay_log),
@@ -804,6 +811,12 @@ class GpuSim(_SimBase):
     def set_replay_log(self, step_logs):
         a = np.ascontiguousarray(step_logs)
         self._check(self.lib.mpenv_set_replay_log(self.h, a.ctypes.data, a.nbytes), "set_replay_log")
+
+    def ray_counts(self, reset=False):
+        """uint64[4]: lidar, line-of-sight, hitscan rays and swept-sphere casts (instrumented build only)."""
+        out = np.zeros(4, np.uint64)
+        self._check(self.lib.mpenv_ray_counts(self.h, out.ctypes.data, int(reset)), "ray_counts")
+        return out
 
     def launches(self):
         a, b = C.c_uint32(), C.c_uint32()

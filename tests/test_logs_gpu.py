@@ -178,3 +178,33 @@ def test_flank_reward_mode_gpu():
         assert np.abs(orc.export("reward")).sum() > 0
     finally:
         gpu.close(); orc.close()
+
+
+def test_ray_census_instrumented_build():
+    """libmpenv_b200_count.so (same sources, -DMPENV_COUNT_RAYS): exact counts where they are
+    known a priori, same simulation results as the product library, and the product refuses."""
+    W, steps = 16, 30
+    cnt = S.GpuSim(W, auto_reset=True, instrumented=True)
+    gpu = S.GpuSim(W, auto_reset=True)
+    try:
+        with pytest.raises(RuntimeError, match="not an instrumented build"):
+            gpu.ray_counts()
+        cnt.init(); gpu.init()
+        cnt.ray_counts(reset=True)
+        fired = 0
+        for s in range(steps):
+            d, a = S.seek_policy(gpu, s, W)
+            for sim in (cnt, gpu):
+                sim.set_actions(d, a)
+                sim.step()
+            ws = [gpu.world_state(w) for w in range(W)]
+            fired += sum(ag["fired_shot_t"] != -np.finfo(np.float32).max for st in ws for ag in st["agents"])
+        for name in S.STEP_OUTPUTS:
+            assert np.array_equal(cnt.export(name).view(np.int32), gpu.export(name).view(np.int32)), name
+        c = cnt.ray_counts()
+        assert c[0] == W * 12 * 80 * steps, "80 lidar rays per agent per step"
+        assert c[2] == fired, "one hitscan ray per shot fired"
+        assert 0 < c[1] <= W * 12 * 24 * steps, "at most 24 line-of-sight rays per agent-step"
+        assert W * 12 * steps <= c[3] <= W * 12 * 11 * steps, "1..11 swept-sphere casts per agent-step"
+    finally:
+        cnt.close(); gpu.close()
