@@ -160,18 +160,13 @@ __device__ __forceinline__ void setRay(RayRegs &r, float ox, float oy, float oz,
 // arithmetic: comp(tri - org, k) == comp(tri, k) - comp(org, k).
 __device__ __forceinline__ bool rayTriangleFast(const FastTri *tri, const RayRegs &r, float t_max, float *out_t)
 {
-    const float4 q0 = reinterpret_cast<const float4 *>(tri)[0];   // ax ay az bx
-    const float4 q1 = reinterpret_cast<const float4 *>(tri)[1];   // by bz cx cy
-    const float4 q2 = reinterpret_cast<const float4 *>(tri)[2];   // cz
-    const float Akx = sel3(r.kx, q0.x, q0.y, q0.z) - r.okx;
-    const float Aky = sel3(r.ky, q0.x, q0.y, q0.z) - r.oky;
-    const float Akz = sel3(r.kz, q0.x, q0.y, q0.z) - r.okz;
-    const float Bkx = sel3(r.kx, q0.w, q1.x, q1.y) - r.okx;
-    const float Bky = sel3(r.ky, q0.w, q1.x, q1.y) - r.oky;
-    const float Bkz = sel3(r.kz, q0.w, q1.x, q1.y) - r.okz;
-    const float Ckx = sel3(r.kx, q1.z, q1.w, q2.x) - r.okx;
-    const float Cky = sel3(r.ky, q1.z, q1.w, q2.x) - r.oky;
-    const float Ckz = sel3(r.kz, q1.z, q1.w, q2.x) - r.okz;
+    // the permuted components come straight from shared memory by index (9 LDS.32) --
+    // 3 LDS.128 + nine two-select sel3 chains cost 27 more issue slots per triangle
+    const float *tk = tri->v;
+    const float *px = tk + r.kx, *py = tk + r.ky, *pz = tk + r.kz;
+    const float Akx = px[0] - r.okx, Aky = py[0] - r.oky, Akz = pz[0] - r.okz;
+    const float Bkx = px[3] - r.okx, Bky = py[3] - r.oky, Bkz = pz[3] - r.okz;
+    const float Ckx = px[6] - r.okx, Cky = py[6] - r.oky, Ckz = pz[6] - r.okz;
 
     const float Ax = fmaf(-r.Sx, Akz, Akx);
     const float Ay = fmaf(-r.Sy, Akz, Aky);
