@@ -68,6 +68,13 @@ __device__ __forceinline__ FastBVH stageFastBVH(const BVHView &g, void *smem)
         c.qMaxX = (float)src.qMaxX[k]; c.qMaxY = (float)src.qMaxY[k]; c.qMaxZ = (float)src.qMaxZ[k];
         c.child = src.children[k];
         c.triSize = src.triSize[k];
+        if (src.children[k] == kBVHSentinel) {
+            // absent child: NaN bounds make the slab test fail by itself (fminf / fmaxf drop the
+            // NaN operand, so t_near = 0 and t_far = NaN, and 0 <= NaN is false) -- no sentinel
+            // compare in the visit
+            const float qnan = __int_as_float(0x7FC00000);
+            c.qMinX = c.qMinY = c.qMinZ = c.qMaxX = c.qMaxY = c.qMaxZ = qnan;
+        }
         sn[n].c[k] = c;
         if (k == 0) {
             sn[n].minX = src.minX; sn[n].minY = src.minY; sn[n].minZ = src.minZ;
@@ -216,8 +223,7 @@ __device__ __forceinline__ float childNear(const FastChild &c, float dqx, float 
         fmaxf(fminf(t_near_z, t_far_z), 0.f)));
     const float t_far3 = fminf(fmaxf(t_far_x, t_near_x), fminf(fmaxf(t_far_y, t_near_y),
         fmaxf(t_far_z, t_near_z)));
-    const bool ok = (c.child != kBVHSentinel) && (t_near <= t_far3);
-    return ok ? t_near : __int_as_float(0x7F800000);
+    return t_near <= t_far3 ? t_near : __int_as_float(0x7F800000);      // absent children carry NaN bounds
 }
 
 // Pool interface (duck-typed):
