@@ -252,7 +252,7 @@ def run_ours(args):
             "sphere_casts_per_s": (round(value * census["sphere_casts"], 1) if census and "rays" in census
                                    else None),
         }
-        print(json.dumps(line))
+        emit(line)
     if world > 1:
         dist.destroy_process_group()
 
@@ -326,7 +326,7 @@ def run_reference(args):
     v = round(worlds * AGENTS * args.steps * steps_per / dt, 1)
     sample = (f"each step = {steps_per} sim steps of {worlds} worlds of the same workload; reference sim code under "
               f"oracle/shim (oracle/_ref/libmpenv_ref.so), {n} host threads")
-    print(json.dumps({
+    emit({
         "impl": "reference", "metric": METRIC, "value": v, "unit": "agent-steps/s",
         "n_gpus": int(os.environ.get("WORLD_SIZE", "1")), "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": round(dt * 1e3 / args.steps, 3), "higher_is_better": True, "scaling": "weak",
@@ -335,10 +335,25 @@ def run_reference(args):
                                "BASELINE.json configs[1])"},
         "cpu_baseline": {"value": v, "unit": "agent-steps/s", "cores": n, "kind": "reference", "sample": sample},
         "e2e": {"value": v, "unit": "agent-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-    }))
+    })
+
+
+_JSON_OUT = None
+
+
+def emit(line):
+    """The ONE JSON line, on the process's original stdout."""
+    _JSON_OUT.write(json.dumps(line) + "\n")
+    _JSON_OUT.flush()
 
 
 def main():
+    # Libraries write to fd 1 behind Python's back (NCCL prints its version banner there when
+    # NCCL_DEBUG is set): keep the original stdout for the JSON line only, send the rest to stderr.
+    global _JSON_OUT
+    sys.stdout.flush()
+    _JSON_OUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=200)
