@@ -10,7 +10,7 @@
 #include <cstdlib>
 
 #include "step_kernels.cuh"
-#include "ray_kernels.cuh"
+#include "lidar_stream.cuh"
 #include "assets.h"
 #include "sim_layout.h"
 #include "../../include/mpenv.h"
@@ -556,6 +556,12 @@ int mpenv_create(const mpenv_config *cfg, mpenv_handle **out)
         if (refill <= 1) h->lidarPoolKernel = batch <= 1 ? k_lidar_pool<1, 1> : k_lidar_pool<10, 1>;
         else if (refill <= 4) h->lidarPoolKernel = batch <= 1 ? k_lidar_pool<1, 4> : k_lidar_pool<10, 4>;
         else h->lidarPoolKernel = batch <= 1 ? k_lidar_pool<1, 8> : k_lidar_pool<10, 8>;
+        // default: the two-task stream (lidar_stream.cuh); MPENV_LIDAR=pool keeps one pool at a time
+        const char *lm = getenv("MPENV_LIDAR");
+        if (!(lm && strcmp(lm, "pool") == 0) && !lb && !rb) {
+            h->lidarPoolKernel = k_lidar_stream<10, 8>;
+            h->lidarPoolSmem = lidarStreamSmemBytes(ka.ctx.bvh.numNodes, ka.ctx.bvh.numTris);
+        }
         MP_CREATE(cudaFuncSetAttribute(h->lidarPoolKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->lidarPoolSmem));
         h->gridLidarPool = gridFor(h, h->lidarPoolKernel, kLidarWarpsPerCTA * 32, h->lidarPoolSmem,
                                    (N / 2) * 32);

@@ -267,3 +267,32 @@ def test_pipelined_readback_equals_sync_read():
             assert np.array_equal(bufs[n].view(np.int32), prev[n].view(np.int32)), n
     finally:
         a_.close(); b_.close()
+
+
+@pytest.mark.parametrize("W", [1, 3, 37, 700])
+def test_lidar_stream_equals_single_pool(W, monkeypatch):
+    """k_lidar_stream (two resident tasks per warp, lidar_stream.cuh) against k_lidar_pool (one
+    160-ray pool at a time) and, at the small sizes, the oracle: warps with no task, one task,
+    an odd number of tasks and a long stream of them."""
+    monkeypatch.setenv("MPENV_LIDAR", "pool")
+    pool = S.GpuSim(W, auto_reset=True)
+    monkeypatch.delenv("MPENV_LIDAR")
+    stream = S.GpuSim(W, auto_reset=True)
+    orc = S.Oracle(W, auto_reset=True, det=True) if W <= 37 else None
+    sims = [s for s in (pool, stream, orc) if s is not None]
+    try:
+        for s in sims:
+            s.init()
+        for step in range(40):
+            d, a = S.random_actions(step, W)
+            for s in sims:
+                s.set_actions(d, a)
+                s.step()
+            for name in ("fwd_lidar", "rear_lidar"):
+                x = stream.export(name).view(np.int32)
+                assert np.array_equal(x, pool.export(name).view(np.int32)), f"step {step}: {name} stream vs pool"
+                if orc is not None:
+                    assert np.array_equal(x, orc.export(name).view(np.int32)), f"step {step}: {name} vs oracle"
+    finally:
+        for s in sims:
+            s.close()
