@@ -28,7 +28,7 @@ struct __align__(16) LidarStreamPool {
                                                      // re-used for its capsule records + directions
     float4 origin[2][4];                             // [buffer][agent * 2 + height]
     float tmesh[2][kLidarTaskRays];                  // closest mesh hit, -1 = miss
-    int32_t st[8];                                   // fin, prep, iss, next_ray, remaining[2] (see k_lidar_stream)
+    int32_t st[12];                                  // fin, prep, iss, next_ray, remaining[2], task[0], 0, task[1]
 };
 static_assert(sizeof(RayTravRec) * 2 * kLidarDirsPerAgent >=
               sizeof(CapsuleRec) * 4 * kAgents + sizeof(float) * 3 * 2 * kLidarDirsPerAgent,
@@ -145,6 +145,27 @@ __device__ __forceinline__ void setRayTrav(RayRegs &r, float4 o, const RayTravRe
     r.tStop = -1.f;                      // closest hit wanted: never stop early
 }
 
+// Next task id from the device-wide counter (>= the task count when they have run out).
+__device__ __forceinline__ int lidarFetchTask(uint32_t *counters)
+{
+    int t = 0;
+    if ((threadIdx.x & 31) == 0) t = (int)atomicAdd(&counters[0], 1u);
+    return __shfl_sync(0xFFFFFFFFu, t, 0);
+}
+
+// The last warp of the grid to finish re-arms the counters for the next launch.
+__device__ __forceinline__ void lidarWarpDone(uint32_t *counters)
+{
+    if ((threadIdx.x & 31) == 0) {
+        __threadfence();
+        const uint32_t total = gridDim.x * kLidarWarpsPerCTA;
+        if (atomicAdd(&counters[1], 1u) == total - 1u) {
+            counters[0] = 0;
+            counters[1] = 0;
+        }
+    }
+}
+
 // Per-lane traversal state (everything that lives across loop iterations).
 #define MP_LANE_STATE(F, I) \
     F(0, r.ox) F(1, r.oy) F(2, r.oz) F(3, r.invX) F(4, r.invY) F(5, r.invZ) F(6, r.Sx) F(7, r.Sy) F(8, r.Sz) \
@@ -157,8 +178,8 @@ __device__ __forceinline__ void setRayTrav(RayRegs &r, float4 o, const RayTravRe
 #define MP_UNSTASH_I(i, x) x = sv[i];
 constexpr int kLaneStateWords = 32;
 
-// Tasks of a warp are numbered 0..n_seq-1 (task id = first + seq * stride) and
-// live in buffer seq & 1.  Warp-uniform stream state:
+// Tasks are handed out by a device-wide counter (warps that draw cheap tasks take more of
+// them); a warp numbers the tasks it draws 0, 1, ... and task seq lives in buffer seq & 1.  Warp-uniform stream state:
 //   fin   oldest task whose export has not run;     prep  tasks set up so far (<= fin + 2)
 //   iss   task whose rays are being handed out;     next_ray  its next ray
 //   remaining0/1  rays of the task in buffer b that have not been retired
@@ -175,22 +196,27 @@ __global__ void __launch_bounds__(kLidarWarpsPerCTA * 32, 3) k_lidar_stream(cons
     const int warp = threadIdx.x >> 5;
     LidarStreamPool &P = pools[warp];
     const int num_tasks = (int)c.cfg.numWorlds * (kAgents / 2);
-    const int first = blockIdx.x * kLidarWarpsPerCTA + warp;
-    const int stride = gridDim.x * kLidarWarpsPerCTA;
-    if (first >= num_tasks) return;                      // no CTA-wide barrier below
-    const int n_seq = (num_tasks - first + stride - 1) / stride;
 
     // stream state lives in shared memory: it is touched only by the refill step, and the
     // traversal loop has no registers to spare (80 at 3 CTAs / SM)
     {
         int32_t prep = 0;
-        for (; prep < 2 && prep < n_seq; prep++) lidarStreamSetup(c, P, prep, first + prep * stride);
+        for (; prep < 2; prep++) {
+            const int task = lidarFetchTask(ka.workCounters);
+            if (task >= num_tasks) break;
+            lidarStreamSetup(c, P, prep, task);
+            if ((threadIdx.x & 31) == 0) P.st[6 + 2 * prep] = task;
+        }
         if ((threadIdx.x & 31) == 0) {
             P.st[0] = 0; P.st[1] = prep; P.st[2] = 0; P.st[3] = 0;
             P.st[4] = kLidarTaskRays; P.st[5] = kLidarTaskRays;
-            P.st[6] = 0; P.st[7] = 0;
+            P.st[7] = 0;
         }
         __syncwarp();
+        if (prep == 0) {
+            lidarWarpDone(ka.workCounters);
+            return;                                      // no CTA-wide barrier below
+        }
     }
 
     const unsigned lane_lt = (1u << (threadIdx.x & 31)) - 1u;
@@ -215,9 +241,6 @@ __global__ void __launch_bounds__(kLidarWarpsPerCTA * 32, 3) k_lidar_stream(cons
         if ((can_issue ? idle_m : fresh_m) != 0 && (__popc(idle_m) >= kRefillBatch || adv_m == 0)) {
             int32_t fin = P.st[0], prep = P.st[1], iss = P.st[2], next_ray = P.st[3];
             int32_t remaining0 = P.st[4], remaining1 = P.st[5];
-            const int first_task = blockIdx.x * kLidarWarpsPerCTA + (threadIdx.x >> 5);
-            const int task_stride = gridDim.x * kLidarWarpsPerCTA;
-            const int num_seq = ((int)c.cfg.numWorlds * (kAgents / 2) - first_task + task_stride - 1) / task_stride;
             // retire finished rays
             const unsigned fresh1_m = __ballot_sync(0xFFFFFFFFu, idle && ray >= 256);
             if (idle && ray >= 0) P.tmesh[ray >> 8][ray & 255] = hit_i ? t_max : -1.f;
@@ -235,15 +258,18 @@ __global__ void __launch_bounds__(kLidarWarpsPerCTA * 32, 3) k_lidar_stream(cons
                     MP_LANE_STATE(MP_STASH_F, MP_STASH_I)
                 }
                 do {
-                    lidarStreamExport(c, P, fin & 1, first_task + fin * task_stride);
+                    lidarStreamExport(c, P, fin & 1, P.st[6 + 2 * (fin & 1)]);
                     fin++;
-                    if (prep < num_seq) {
-                        lidarStreamSetup(c, P, prep & 1, first_task + prep * task_stride);
+                    // fin + 1 == prep, or the tasks have run out (then no further fetch: prep stays)
+                    const int task = fin + 1 == prep ? lidarFetchTask(ka.workCounters) : num_tasks;
+                    if (task < num_tasks) {
+                        lidarStreamSetup(c, P, prep & 1, task);
+                        if ((threadIdx.x & 31) == 0) P.st[6 + 2 * (prep & 1)] = task;
                         if (prep & 1) remaining1 = kLidarTaskRays; else remaining0 = kLidarTaskRays;
                         prep++;
                     }
                 } while (fin < prep && ((fin & 1) ? remaining1 : remaining0) == 0);
-                if (fin >= num_seq) break;
+                if (fin >= prep) break;                  // nothing resident and nothing left to fetch
                 {
                     const int32_t *sv = stack + 32 + *reinterpret_cast<volatile int32_t *>(&P.st[7]);
                     MP_LANE_STATE(MP_UNSTASH_F, MP_UNSTASH_I)
@@ -331,6 +357,7 @@ __global__ void __launch_bounds__(kLidarWarpsPerCTA * 32, 3) k_lidar_stream(cons
             leaf = -1;
         }
     }
+    lidarWarpDone(ka.workCounters);
 }
 
 inline size_t lidarStreamSmemBytes(uint32_t num_nodes, uint32_t num_tris)

@@ -509,6 +509,7 @@ int mpenv_create(const mpenv_config *cfg, mpenv_handle **out)
     ka.bvhVertWords = (uint32_t)(vert_bytes / 4);
     h->bvhSmemBytes = node_bytes + ((vert_bytes + 15) / 16) * 16;
     ka.bvhInSmem = h->bvhSmemBytes <= 160 * 1024 ? 1 : 0;
+    if (!devAlloc((void **)&ka.workCounters, 64)) return bail(MPENV_ERR_CUDA);
     if (!ka.bvhInSmem) h->bvhSmemBytes = 0;
 
     // TrainControl from the flags (mgr.cpp:1397-1413)

@@ -30,6 +30,7 @@ struct KernelArgs {
     uint32_t bvhNodeWords;   // 32-bit words of node data
     uint32_t bvhVertWords;   // 32-bit words of vertex data (incl. the pad triangle)
     int32_t bvhInSmem;       // 1: stage into shared memory, 0: traverse from global / L2
+    uint32_t *workCounters;  // device-wide task counters of the dynamically scheduled kernels (zero between launches)
 };
 
 // Copies the BVH into dynamic shared memory and returns a view onto it.
