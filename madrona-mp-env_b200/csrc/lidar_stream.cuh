@@ -145,27 +145,6 @@ __device__ __forceinline__ void setRayTrav(RayRegs &r, float4 o, const RayTravRe
     r.tStop = -1.f;                      // closest hit wanted: never stop early
 }
 
-// Next task id from the device-wide counter (>= the task count when they have run out).
-__device__ __forceinline__ int lidarFetchTask(uint32_t *counters)
-{
-    int t = 0;
-    if ((threadIdx.x & 31) == 0) t = (int)atomicAdd(&counters[0], 1u);
-    return __shfl_sync(0xFFFFFFFFu, t, 0);
-}
-
-// The last warp of the grid to finish re-arms the counters for the next launch.
-__device__ __forceinline__ void lidarWarpDone(uint32_t *counters)
-{
-    if ((threadIdx.x & 31) == 0) {
-        __threadfence();
-        const uint32_t total = gridDim.x * kLidarWarpsPerCTA;
-        if (atomicAdd(&counters[1], 1u) == total - 1u) {
-            counters[0] = 0;
-            counters[1] = 0;
-        }
-    }
-}
-
 // Per-lane traversal state (everything that lives across loop iterations).
 #define MP_LANE_STATE(F, I) \
     F(0, r.ox) F(1, r.oy) F(2, r.oz) F(3, r.invX) F(4, r.invY) F(5, r.invZ) F(6, r.Sx) F(7, r.Sy) F(8, r.Sz) \
@@ -202,7 +181,7 @@ __global__ void __launch_bounds__(kLidarWarpsPerCTA * 32, 3) k_lidar_stream(cons
     {
         int32_t prep = 0;
         for (; prep < 2; prep++) {
-            const int task = lidarFetchTask(ka.workCounters);
+            const int task = fetchWarpTask(ka.workCounters);
             if (task >= num_tasks) break;
             lidarStreamSetup(c, P, prep, task);
             if ((threadIdx.x & 31) == 0) P.st[6 + 2 * prep] = task;
@@ -214,7 +193,7 @@ __global__ void __launch_bounds__(kLidarWarpsPerCTA * 32, 3) k_lidar_stream(cons
         }
         __syncwarp();
         if (prep == 0) {
-            lidarWarpDone(ka.workCounters);
+            warpTasksDone(ka.workCounters, gridDim.x * kLidarWarpsPerCTA);
             return;                                      // no CTA-wide barrier below
         }
     }
@@ -261,7 +240,7 @@ __global__ void __launch_bounds__(kLidarWarpsPerCTA * 32, 3) k_lidar_stream(cons
                     lidarStreamExport(c, P, fin & 1, P.st[6 + 2 * (fin & 1)]);
                     fin++;
                     // fin + 1 == prep, or the tasks have run out (then no further fetch: prep stays)
-                    const int task = fin + 1 == prep ? lidarFetchTask(ka.workCounters) : num_tasks;
+                    const int task = fin + 1 == prep ? fetchWarpTask(ka.workCounters) : num_tasks;
                     if (task < num_tasks) {
                         lidarStreamSetup(c, P, prep & 1, task);
                         if ((threadIdx.x & 31) == 0) P.st[6 + 2 * (prep & 1)] = task;
@@ -357,7 +336,7 @@ __global__ void __launch_bounds__(kLidarWarpsPerCTA * 32, 3) k_lidar_stream(cons
             leaf = -1;
         }
     }
-    lidarWarpDone(ka.workCounters);
+    warpTasksDone(ka.workCounters, gridDim.x * kLidarWarpsPerCTA);
 }
 
 inline size_t lidarStreamSmemBytes(uint32_t num_nodes, uint32_t num_tris)

@@ -201,7 +201,9 @@ __global__ void __launch_bounds__(kLosWarpsPerCTA * 32, 2) k_los_pool(KernelArgs
     const float *fr = c.mc->frustum;
     const int W = (int)c.cfg.numWorlds;
 
-    for (int w = blockIdx.x * kLosWarpsPerCTA + warp; w < W; w += gridDim.x * kLosWarpsPerCTA) {
+    for (;;) {
+        const int w = fetchWarpTask(ka.workCounters + 2);
+        if (w >= W) break;
         const int base = w * kAgents;
         // ---- per-agent terms (utils.cpp:240-251)
         if (lane < 4) P.seen[lane] = 0;
@@ -319,6 +321,7 @@ __global__ void __launch_bounds__(kLosWarpsPerCTA * 32, 2) k_los_pool(KernelArgs
         }
         __syncwarp();
     }
+    warpTasksDone(ka.workCounters + 2, gridDim.x * kLosWarpsPerCTA);
 }
 
 inline size_t losPoolSmemBytes(uint32_t num_nodes, uint32_t num_tris)

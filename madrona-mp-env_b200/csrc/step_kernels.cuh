@@ -33,6 +33,30 @@ struct KernelArgs {
     uint32_t *workCounters;  // device-wide task counters of the dynamically scheduled kernels (zero between launches)
 };
 
+// ---- dynamic task hand-out --------------------------------------------------
+// A kernel whose tasks vary in cost draws them from a device-wide counter pair
+// {next task, warps finished} (KernelArgs::workCounters, zero between launches)
+// instead of a static stride: warps that get cheap tasks take more of them.
+// Returns the next task id (>= the task count once they have run out).
+__device__ __forceinline__ int fetchWarpTask(uint32_t *pair)
+{
+    int t = 0;
+    if ((threadIdx.x & 31) == 0) t = (int)atomicAdd(&pair[0], 1u);
+    return __shfl_sync(0xFFFFFFFFu, t, 0);
+}
+
+// Every warp of the grid calls this once, after its last fetch; the last one re-arms the pair.
+__device__ __forceinline__ void warpTasksDone(uint32_t *pair, uint32_t total_warps)
+{
+    if ((threadIdx.x & 31) == 0) {
+        __threadfence();
+        if (atomicAdd(&pair[1], 1u) == total_warps - 1u) {
+            pair[0] = 0;
+            pair[1] = 0;
+        }
+    }
+}
+
 // Copies the BVH into dynamic shared memory and returns a view onto it.
 __device__ __forceinline__ BVHView stageBVH(const KernelArgs &ka, uint32_t *smem)
 {
@@ -84,8 +108,16 @@ __global__ void __launch_bounds__(128) k_move(KernelArgs ka)
     Ctx c = ka.ctx;
     c.bvh = stageBVH(ka, reinterpret_cast<uint32_t *>(smem_raw));
     const int N = (int)c.cfg.numWorlds * kAgents;
-    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < N; i += gridDim.x * blockDim.x)
-        stageMove(c, i);
+    // 1 .. 11 sphere casts per agent: 32-agent chunks are drawn dynamically (a static stride
+    // gave 1.3 agents per thread, i.e. a second, 30 %-full round)
+    const int chunks = (N + 31) / 32;
+    for (;;) {
+        const int chunk = fetchWarpTask(ka.workCounters + 4);
+        if (chunk >= chunks) break;
+        const int i = chunk * 32 + (int)(threadIdx.x & 31);
+        if (i < N) stageMove(c, i);
+    }
+    warpTasksDone(ka.workCounters + 4, gridDim.x * (blockDim.x >> 5));
 }
 
 template <bool kCold>
