@@ -13,6 +13,14 @@
 
 namespace mpenv {
 
+#ifndef MPENV_STREAM_WARPS
+// one CTA of 28 warps per SM: 72 registers x 896 threads fills the register file, 206 KB of
+// shared memory (BVH staged once per SM); measured against 3 CTAs x 8 warps: 1.243 -> 1.165 ms
+#define MPENV_STREAM_WARPS 28
+#define MPENV_STREAM_MINB 1
+#endif
+constexpr int kStreamWarpsPerCTA = MPENV_STREAM_WARPS;
+
 // The traversal half of RayDirRec; the direction itself is only needed by the
 // capsule phase and is recomputed there (same expressions, see lidarDir).
 struct __align__(16) RayTravRec {
@@ -165,7 +173,7 @@ constexpr int kLaneStateWords = 32;
 // (kept in LidarStreamPool::st).  The node visit / child walk / leaf test are traversePool's, statement for
 // statement (ray_fast.cuh); only the refill step knows about tasks.
 template <int kLeafBatch, int kRefillBatch>
-__global__ void __launch_bounds__(kLidarWarpsPerCTA * 32, 3) k_lidar_stream(const __grid_constant__ KernelArgs ka)
+__global__ void __launch_bounds__(kStreamWarpsPerCTA * 32, MPENV_STREAM_MINB) k_lidar_stream(const __grid_constant__ KernelArgs ka)
 {
     extern __shared__ uint4 smem_raw[];
     const Ctx &c = ka.ctx;
@@ -193,7 +201,7 @@ __global__ void __launch_bounds__(kLidarWarpsPerCTA * 32, 3) k_lidar_stream(cons
         }
         __syncwarp();
         if (prep == 0) {
-            warpTasksDone(ka.workCounters, gridDim.x * kLidarWarpsPerCTA);
+            warpTasksDone(ka.workCounters, gridDim.x * kStreamWarpsPerCTA);
             return;                                      // no CTA-wide barrier below
         }
     }
@@ -336,12 +344,12 @@ __global__ void __launch_bounds__(kLidarWarpsPerCTA * 32, 3) k_lidar_stream(cons
             leaf = -1;
         }
     }
-    warpTasksDone(ka.workCounters, gridDim.x * kLidarWarpsPerCTA);
+    warpTasksDone(ka.workCounters, gridDim.x * kStreamWarpsPerCTA);
 }
 
 inline size_t lidarStreamSmemBytes(uint32_t num_nodes, uint32_t num_tris)
 {
-    return fastBVHBytes(num_nodes, num_tris) + kLidarWarpsPerCTA * sizeof(LidarStreamPool);
+    return fastBVHBytes(num_nodes, num_tris) + kStreamWarpsPerCTA * sizeof(LidarStreamPool);
 }
 
 }  // namespace mpenv

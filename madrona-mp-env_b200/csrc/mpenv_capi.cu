@@ -56,6 +56,7 @@ struct mpenv_handle {
     bool poolLidar = false;                  // warp-pooled ray engine (ray_kernels.cuh)
     size_t lidarPoolSmem = 0;
     int gridLidarPool = 0;
+    int lidarBlock = kLidarWarpsPerCTA * 32;
     void (*lidarPoolKernel)(KernelArgs) = nullptr;
     bool poolLos = false;
     size_t losPoolSmem = 0;
@@ -117,7 +118,7 @@ int gridFor(mpenv_handle *h, K kernel, int block, size_t smem, long long items)
 
 void launchLidar(mpenv_handle *h, cudaStream_t s)
 {
-    if (h->poolLidar) h->lidarPoolKernel<<<h->gridLidarPool, kLidarWarpsPerCTA * 32, h->lidarPoolSmem, s>>>(h->ka);
+    if (h->poolLidar) h->lidarPoolKernel<<<h->gridLidarPool, h->lidarBlock, h->lidarPoolSmem, s>>>(h->ka);
     else k_lidar<<<h->gridLidar, 160, h->bvhSmemBytes, s>>>(h->ka);
 }
 
@@ -562,9 +563,10 @@ int mpenv_create(const mpenv_config *cfg, mpenv_handle **out)
         if (!(lm && strcmp(lm, "pool") == 0) && !lb && !rb) {
             h->lidarPoolKernel = k_lidar_stream<10, 8>;
             h->lidarPoolSmem = lidarStreamSmemBytes(ka.ctx.bvh.numNodes, ka.ctx.bvh.numTris);
+            h->lidarBlock = kStreamWarpsPerCTA * 32;
         }
         MP_CREATE(cudaFuncSetAttribute(h->lidarPoolKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->lidarPoolSmem));
-        h->gridLidarPool = gridFor(h, h->lidarPoolKernel, kLidarWarpsPerCTA * 32, h->lidarPoolSmem,
+        h->gridLidarPool = gridFor(h, h->lidarPoolKernel, h->lidarBlock, h->lidarPoolSmem,
                                    (N / 2) * 32);
     }
 
