@@ -20,6 +20,10 @@ namespace mpenv {
 #define MPENV_STREAM_MINB 1
 #endif
 constexpr int kStreamWarpsPerCTA = MPENV_STREAM_WARPS;
+#ifndef MPENV_STREAM_LEAF
+#define MPENV_STREAM_LEAF 10      // leaf-test / refill batch thresholds (see traversePool)
+#define MPENV_STREAM_REFILL 8
+#endif
 
 // The traversal half of RayDirRec; the direction itself is only needed by the
 // capsule phase and is recomputed there (same expressions, see lidarDir).

@@ -561,7 +561,7 @@ int mpenv_create(const mpenv_config *cfg, mpenv_handle **out)
         // default: the two-task stream (lidar_stream.cuh); MPENV_LIDAR=pool keeps one pool at a time
         const char *lm = getenv("MPENV_LIDAR");
         if (!(lm && strcmp(lm, "pool") == 0) && !lb && !rb) {
-            h->lidarPoolKernel = k_lidar_stream<10, 8>;
+            h->lidarPoolKernel = k_lidar_stream<MPENV_STREAM_LEAF, MPENV_STREAM_REFILL>;
             h->lidarPoolSmem = lidarStreamSmemBytes(ka.ctx.bvh.numNodes, ka.ctx.bvh.numTris);
             h->lidarBlock = kStreamWarpsPerCTA * 32;
         }
