@@ -760,6 +760,27 @@ float ref_sphere_cast_brute(void *h, const float *o, const float *d, float r)
 }
 
 // rand::split_i / sampleI32 / sampleUniform probes for the Threefry KATs.
+// Batched probes (one C loop instead of one ctypes call per ray): the >= 10^6-ray
+// brute-force pins of tests/test_oracle_pins.py.  mode 0 = traversal, 1 = brute force.
+void ref_trace_rays(void *h, int64_t n, const float *o, const float *d, int32_t mode,
+                    float *t_out, int32_t *hit_out)
+{
+    for (int64_t i = 0; i < n; i++) {
+        hit_out[i] = mode == 0 ? ref_trace_ray(h, o + 3 * i, d + 3 * i, FLT_MAX, t_out + i)
+                               : ref_trace_ray_brute(h, o + 3 * i, d + 3 * i, t_out + i);
+    }
+}
+
+// normal_out [n][3]: in = the caller's initial normal, out = contact normal (untouched on a miss)
+void ref_sphere_casts(void *h, int64_t n, const float *o, const float *d, float r, int32_t mode,
+                      float *t_out, float *normal_out)
+{
+    for (int64_t i = 0; i < n; i++) {
+        t_out[i] = mode == 0 ? ref_sphere_cast(h, o + 3 * i, d + 3 * i, r, normal_out + 3 * i)
+                             : ref_sphere_cast_brute(h, o + 3 * i, d + 3 * i, r);
+    }
+}
+
 void ref_rand_split(uint32_t a, uint32_t b, uint32_t idx, uint32_t idx_upper, uint32_t *out)
 {
     RandKey k = rand::split_i(RandKey { a, b }, idx, idx_upper);

@@ -250,6 +250,16 @@ float hostsim_sphere_cast(void *h, const float *o, const float *d, float r, floa
     return t;
 }
 
+void hostsim_trace_rays(void *h, int64_t n, const float *o, const float *d, float *t_out, int32_t *hit_out)
+{
+    for (int64_t i = 0; i < n; i++) hit_out[i] = hostsim_trace_ray(h, o + 3 * i, d + 3 * i, t_out + i);
+}
+
+void hostsim_sphere_casts(void *h, int64_t n, const float *o, const float *d, float r, float *t_out, float *n_io)
+{
+    for (int64_t i = 0; i < n; i++) t_out[i] = hostsim_sphere_cast(h, o + 3 * i, d + 3 * i, r, n_io + 3 * i);
+}
+
 void hostsim_rand_split(uint32_t a, uint32_t b, uint32_t idx, uint32_t idx_upper, uint32_t *out)
 {
     RandKey k; k.a = a; k.b = b;

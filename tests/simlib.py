@@ -506,6 +506,22 @@ class Oracle(_SimBase):
         o = np.asarray(o, np.float32); d = np.asarray(d, np.float32)
         return self.lib.ref_sphere_cast_brute(self.h, o.ctypes.data, d.ctypes.data, r)
 
+    def trace_rays(self, o, d, brute=False):
+        """Batched traceRay (mesh_bvh.inl:110-208) / brute force over all triangles: (hit i32[n], t f32[n])."""
+        o = np.ascontiguousarray(o, np.float32); d = np.ascontiguousarray(d, np.float32)
+        t = np.empty(len(o), np.float32); hit = np.empty(len(o), np.int32)
+        self.lib.ref_trace_rays.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p]
+        self.lib.ref_trace_rays(self.h, len(o), o.ctypes.data, d.ctypes.data, int(brute), t.ctypes.data, hit.ctypes.data)
+        return hit, t
+
+    def sphere_casts(self, o, d, r=15.0, brute=False):
+        o = np.ascontiguousarray(o, np.float32); d = np.ascontiguousarray(d, np.float32)
+        t = np.empty(len(o), np.float32); n = np.zeros((len(o), 3), np.float32)
+        self.lib.ref_sphere_casts.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_float, C.c_int32,
+                                              C.c_void_p, C.c_void_p]
+        self.lib.ref_sphere_casts(self.h, len(o), o.ctypes.data, d.ctypes.data, r, int(brute), t.ctypes.data, n.ctypes.data)
+        return t, n
+
 
 # ------------------------------------------------------------------ hostsim
 class HostSimConfig(C.Structure):
@@ -600,6 +616,21 @@ class HostSim(_SimBase):
         o = np.asarray(o, np.float32); d = np.asarray(d, np.float32)
         n = np.zeros(3, np.float32)
         t = self.lib.hostsim_sphere_cast(self.h, o.ctypes.data, d.ctypes.data, r, n.ctypes.data)
+        return t, n
+
+    def trace_rays(self, o, d):
+        o = np.ascontiguousarray(o, np.float32); d = np.ascontiguousarray(d, np.float32)
+        t = np.empty(len(o), np.float32); hit = np.empty(len(o), np.int32)
+        self.lib.hostsim_trace_rays.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        self.lib.hostsim_trace_rays(self.h, len(o), o.ctypes.data, d.ctypes.data, t.ctypes.data, hit.ctypes.data)
+        return hit, t
+
+    def sphere_casts(self, o, d, r=15.0):
+        o = np.ascontiguousarray(o, np.float32); d = np.ascontiguousarray(d, np.float32)
+        t = np.empty(len(o), np.float32); n = np.zeros((len(o), 3), np.float32)
+        self.lib.hostsim_sphere_casts.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_float,
+                                                  C.c_void_p, C.c_void_p]
+        self.lib.hostsim_sphere_casts(self.h, len(o), o.ctypes.data, d.ctypes.data, r, t.ctypes.data, n.ctypes.data)
         return t, n
 
 

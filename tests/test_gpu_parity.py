@@ -48,8 +48,38 @@ def random_policy(sim, s, W):
 
 
 def test_random_actions_32_worlds_bit_exact():
-    # BASELINE.json configs[0], shortened: 32 worlds, random actions
-    rollout(32, 200, random_policy, check_every=20)
+    # BASELINE.json configs[0] at its full length: 32 worlds, random actions, 1000 steps
+    rollout(32, 1000, random_policy, check_every=50)
+
+
+def test_gpu_vs_libm_reference_every_step():
+    """The parity bridge (tests/bridge.py): the CUDA path against the UNMODIFIED-arithmetic
+    reference (libm oracle), configs[0] at full length, every step: integer exports
+    bit-identical, floats within 1e-4 * max(1, |row|_inf) up to the committed budget of
+    lidar discontinuity flips (reference sim.cpp:3439-3500, utils.cpp:10-72)."""
+    import bridge
+    stats = bridge.run_bridge(lambda: S.GpuSim(32), W=32, steps=1000)
+    stats.check_budgets()
+
+
+def test_forced_reset_and_episode_end_gpu():
+    """triggerReset mid-episode (mgr.cpp:2484-2500) on some worlds, then 40 more steps."""
+    W = 6
+    gpu = S.GpuSim(W, auto_reset=True)
+    orc = S.Oracle(W, auto_reset=True, det=True)
+    try:
+        gpu.init(); orc.init()
+        for s in range(70):
+            d, a = S.random_actions(s, W)
+            if s == 30:
+                for sim in (gpu, orc):
+                    sim.set_export("reset", np.array([[0], [1], [0], [1], [1], [0]], np.int32))
+            for sim in (gpu, orc):
+                sim.set_actions(d, a); sim.step()
+            assert_same(gpu, orc, W, f"step {s}")
+        assert orc.world_state(1)["cur_step"] < 45 and orc.world_state(0)["cur_step"] >= 70
+    finally:
+        gpu.close(); orc.close()
 
 
 def test_combat_policy_bit_exact():
@@ -98,16 +128,23 @@ def test_large_batch_properties():
         assert np.all(flags.sum(axis=1) == (depth != -1)), "exactly one class flag per hit"
         sp = gpu.export("self_pos")
         assert np.all((sp >= 0) & (sp <= 1))
-        # the first 32 worlds of the big batch equal a 32-world oracle run
-        orc = S.Oracle(32, auto_reset=True, det=True, num_threads=0)
-        orc.init()
-        for s in range(20):
-            d, a = S.random_actions(s, 32)
-            orc.set_actions(d, a); orc.step()
-        for name in ("self_obs", "fwd_lidar", "reward", "opponent_obs"):
-            x, y = gpu.export(name), orc.export(name)
-            assert np.array_equal(x[:len(y)].view(np.int32), y.view(np.int32)), name
-        orc.close()
+        # oracle shards (world_id_offset) against the big batch: the first CTAs, the middle and
+        # the very end of the batch (the dynamic task counters' tail), every exported tensor
+        acts = [S.random_actions(s, W) for s in range(20)]
+        for off, n in ((0, 32), (4095, 16), (8160, 32)):
+            orc = S.Oracle(n, auto_reset=True, det=True, num_threads=0, world_id_offset=off)
+            orc.init()
+            for s in range(20):
+                d, a = acts[s]
+                orc.set_actions(d[off * 12:(off + n) * 12], a[off * 12:(off + n) * 12]); orc.step()
+            for name in S.STEP_OUTPUTS:
+                x, y = gpu.export(name), orc.export(name)
+                per = len(y) // n
+                assert np.array_equal(x[off * per:(off + n) * per].view(np.int32), y.view(np.int32)), (off, name)
+            for w in (0, n - 1):
+                dd = S.diff_world_state(gpu.world_state(off + w), orc.world_state(w))
+                assert not dd, f"world {off + w}: {dd[:8]}"
+            orc.close()
     finally:
         gpu.close()
 

@@ -131,26 +131,17 @@ def test_golden_fixture(built):
 
 
 def test_libm_oracle_within_tolerance(built):
-    """The det oracle differs from the libm oracle (the reference's own arithmetic)
-    only through <= 2 ulp transcendentals.  north_star bar: integer state identical,
-    floats within 1e-4 relative.  Tolerance used: |x - y| <= 1e-4 * max(1, |row|_inf)
-    (body-frame velocity components are un-normalised, up to 400, so a component
-    near zero is judged against its vector's magnitude).  Measured in this container:
-    integer state identical and positions within 2e-6 for all 32 worlds over 400
-    steps of the random-action stream."""
-    W = 32
-    a_, b_ = S.Oracle(W, det=True, num_threads=0), S.Oracle(W, det=False, num_threads=0)
-    try:
-        a_.init(); b_.init()
-        for s in range(200):
-            d, a = S.random_actions(s, W)
-            for sim in (a_, b_):
-                sim.set_actions(d, a); sim.step()
-        for name in ("hp", "alive", "magazine", "done", "match_result", "opponent_masks"):
-            assert np.array_equal(a_.export(name), b_.export(name)), name
-        for name in ("self_obs", "self_pos", "reward", "teammate_obs", "opponent_obs", "fwd_lidar"):
-            x, y = a_.export(name), b_.export(name)
-            scale = np.maximum(1.0, np.abs(y).max(axis=1, keepdims=True))
-            assert (np.abs(x - y) <= 1e-4 * scale).all(), f"{name}: max abs diff {np.abs(x - y).max()}"
-    finally:
-        a_.close(); b_.close()
+    """The det oracle (the checker of every bit-exact test) against the libm oracle (the
+    reference's own arithmetic), BASELINE.json configs[0]: 32 worlds x 1000 steps of the
+    random-action stream, compared EVERY step (tests/bridge.py).  The two differ only
+    through <= 2 ulp transcendentals.  north_star bar: integer exports identical;
+    floats within 1e-4 * max(1, |row|_inf) except a counted set of discontinuity flips
+    (a lidar ray grazing a silhouette edge lands on another surface), budgets in
+    bridge.FLIP_BUDGET.  Measured in this container: integer exports identical for all
+    1000 steps; fwd_lidar 7.8e-4 of rays outside the tolerance (first at step 38),
+    rear_lidar 1.6e-4, every other tensor <= 5.2e-6 of its elements (first at step 205).
+    The same comparison runs against the CUDA path in test_gpu_parity.py."""
+    import bridge
+    stats = bridge.run_bridge(lambda: S.Oracle(32, det=True, num_threads=0), W=32, steps=1000)
+    stats.check_budgets()
+    assert stats.flips["fwd_lidar"] > 0, "no discontinuity flip in 1000 steps: the comparison is not seeing the lidar"

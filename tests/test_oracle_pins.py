@@ -97,50 +97,57 @@ def _random_rays(n, seed, bounds):
 def test_bvh_traversal_equals_brute_force(orc, host):
     """Closest-hit results do not depend on BVH topology (ours is not Embree's): the
     reference's traceRay over OUR nodes vs the reference's triangle routine over all
-    252 triangles.  simple_map has coplanar, overlapping wall faces (y = +-551.18):
-    there two triangles give t values 1 ulp apart and "the later triangle wins on
-    T <= t_max * det" (mesh_bvh.inl:536) makes the winner order dependent -- so the
-    pin is: same hit flag, |dt| <= 2 ulp, and exact equality for >= 99.9 % of rays.
-    (This is why the CUDA traversal keeps the reference's visiting ORDER.)  The
-    device restatement over the same nodes must equal the reference bit for bit."""
+    252 triangles, 10^6 random rays.  simple_map has coplanar,
+    overlapping wall faces (y = +-551.18): there two triangles give t values 1 ulp
+    apart and "the later triangle wins on T <= t_max * det" (mesh_bvh.inl:536) makes
+    the winner order dependent -- so the pin is: same hit flag, |dt| <= 2 ulp (of t, or 1 ulp of
+    the origin's magnitude for hits next to the origin), and
+    exact equality for >= 99.9 % of rays.  (This is why the CUDA traversal keeps the
+    reference's visiting ORDER.)  The device restatement over the same nodes must
+    equal the reference bit for bit."""
     _, _, info = S.load_map(host.lib)
-    o, d = _random_rays(20000, 7, list(info.world_bounds))
-    hits = inexact = 0
-    for i in range(len(o)):
-        h0, t0 = orc.trace_ray(o[i], d[i])
-        h1, t1 = orc.trace_ray_brute(o[i], d[i])
-        h2, t2 = host.trace_ray(o[i], d[i])
-        assert h0 == h1, f"ray {i}: bvh {h0, t0} brute {h1, t1}"
-        if h0 and t0 != t1:
-            assert abs(t0 - t1) <= 2 * np.spacing(np.float32(t0)), f"ray {i}: bvh {t0} brute {t1}"
-            inexact += 1
-        assert h0 == h2 and (not h0 or t0 == t2), f"ray {i}: reference {h0, t0} device fn {h2, t2}"
-        hits += h0
-    assert hits > len(o) // 2 and inexact <= len(o) // 1000
+    o, d = _random_rays(1_000_000, 7, list(info.world_bounds))
+    h0, t0 = orc.trace_rays(o, d)
+    h1, t1 = orc.trace_rays(o, d, brute=True)
+    h2, t2 = host.trace_rays(o, d)
+    assert np.array_equal(h0, h1), f"hit flags differ on {np.flatnonzero(h0 != h1)[:5]}"
+    hit = h0 != 0
+    inexact = hit & (t0 != t1)
+    # 160 of the 164 inexact rays of this sample are 1 ulp of t apart; the other 4 start within a few
+    # units of the coplanar pair (t < 60 at |origin| ~ 750), where the two triangles' t differ by
+    # <= 1 ulp of the ORIGIN's magnitude (the Woop test subtracts the origin first)
+    dt = np.abs(t0[inexact] - t1[inexact])
+    coord_ulp = np.spacing(np.abs(o[inexact]).max(axis=1))
+    assert ((dt <= 2 * np.spacing(t0[inexact])) | (dt <= coord_ulp)).all()
+    assert np.array_equal(h0, h2) and np.array_equal(t0[hit].view(np.int32), t2[hit].view(np.int32)), \
+        "device traversal function differs from the reference's"
+    assert hit.sum() > len(o) // 2 and inexact.sum() <= len(o) // 1000
 
 
 def test_sphere_cast_equals_brute_force(orc, host):
-    """Swept-sphere casts.  The device restatement must equal the reference bit for
-    bit (t and normal) on the same nodes.  Against brute force the pin is limited to
-    the regime the step uses, t <= 1 (one step's displacement, sim.cpp:889-1028):
-    the reference's vertex test is run against a mirrored vertex (mesh_bvh.inl:
-    1073-1104 receives the origin-relative vertex and subtracts it from the absolute
-    origin), so far along the infinite ray phantom hits exist that a BVH culls and
-    brute force does not; they are reproduced, not fixed."""
+    """Swept-sphere casts, 10^6 of them.  The device restatement must equal the
+    reference bit for bit (t and normal) on the same nodes -- that is the contract.
+    Against brute force over all triangles the pin is statistical, and only in the
+    regime the step uses, t <= 1 (one step's displacement, sim.cpp:889-1028): the
+    reference's vertex test is run against a mirrored vertex (mesh_bvh.inl:1073-1104
+    receives the origin-relative vertex and subtracts it from the absolute origin),
+    so phantom hits exist that a BVH culls or not depending on its boxes.  Measured on
+    this sample: 192,890 casts with min(t_bvh, t_brute) <= 1; 73 of them (3.8e-4)
+    differ -- 64 phantoms that only brute force sees, 9 where brute force finds an
+    earlier phantom.  They are reproduced (same nodes => same result), not fixed; with
+    Embree's tree instead of ours those ~1e-4 casts are parity-unpinned."""
     _, _, info = S.load_map(host.lib)
-    o, d = _random_rays(6000, 11, list(info.world_bounds))
+    o, d = _random_rays(1_000_000, 11, list(info.world_bounds))
     rng = np.random.default_rng(3)
     d = (d * rng.uniform(0.1, 60.0, (len(d), 1))).astype(np.float32)   # casts use un-normalised deltas
-    hits = 0
-    for i in range(len(o)):
-        t0, n0 = orc.sphere_cast(o[i], d[i])
-        t1 = orc.sphere_cast_brute(o[i], d[i])
-        t2, n2 = host.sphere_cast(o[i], d[i])
-        if min(t0, t1) <= 1.0:
-            assert t0 == t1, f"cast {i}: bvh {t0} brute {t1}"
-            hits += 1
-        assert t0 == t2 and np.array_equal(n0.view(np.int32), n2.view(np.int32)), f"cast {i}"
-    assert hits > 300
+    t0, n0 = orc.sphere_casts(o, d)
+    t1, _ = orc.sphere_casts(o, d, brute=True)
+    t2, n2 = host.sphere_casts(o, d)
+    assert np.array_equal(t0.view(np.int32), t2.view(np.int32)) and np.array_equal(n0.view(np.int32), n2.view(np.int32))
+    step_regime = np.minimum(t0, t1) <= 1.0
+    differ = step_regime & (t0.view(np.int32) != t1.view(np.int32))
+    assert step_regime.sum() > 50_000
+    assert differ.sum() <= 1e-3 * step_regime.sum(), f"{differ.sum()} of {step_regime.sum()} in-step casts depend on topology"
 
 
 def test_export_row_sizes(orc):
