@@ -28,10 +28,9 @@ constexpr int kStreamWarpsPerCTA = MPENV_STREAM_WARPS;
 // The traversal half of RayDirRec; the direction itself is only needed by the
 // capsule phase and is recomputed there (same expressions, see lidarDir).
 struct __align__(16) RayTravRec {
-    float invX, invY, invZ, Sx;
-    float Sy, Sz;
-    int32_t kperm;
+    float invX, invY, invZ;
     int32_t pad;
+    RayTriRec tri;
 };
 static_assert(sizeof(RayTravRec) == 32, "RayTravRec is 2 x 16 bytes");
 
@@ -84,8 +83,8 @@ __device__ __noinline__ void lidarStreamSetup(const Ctx &c, LidarStreamPool &P, 
         const RayDirRec r = makeRayDirRec(lidarDir(c, idx0, d));
         RayTravRec t;
         t.invX = r.invX; t.invY = r.invY; t.invZ = r.invZ;
-        t.Sx = r.Sx; t.Sy = r.Sy; t.Sz = r.Sz;
-        t.kperm = r.kperm; t.pad = 0;
+        t.pad = 0;
+        t.tri = r.tri;
         P.trav[b][d] = t;
     }
     if (lane == 0) MP_COUNT_RAYS(0, kLidarTaskRays);
@@ -145,29 +144,16 @@ __device__ __noinline__ void lidarStreamExport(const Ctx &c, LidarStreamPool &P,
     __syncwarp();
 }
 
-__device__ __forceinline__ void setRayTrav(RayRegs &r, float4 o, const RayTravRec &d)
-{
-    r.ox = o.x; r.oy = o.y; r.oz = o.z;
-    r.invX = d.invX; r.invY = d.invY; r.invZ = d.invZ;
-    r.Sx = d.Sx; r.Sy = d.Sy; r.Sz = d.Sz;
-    r.kx = d.kperm & 3; r.ky = (d.kperm >> 2) & 3; r.kz = (d.kperm >> 4) & 3;
-    r.okx = sel3(r.kx, o.x, o.y, o.z);
-    r.oky = sel3(r.ky, o.x, o.y, o.z);
-    r.okz = sel3(r.kz, o.x, o.y, o.z);
-    r.tStop = -1.f;                      // closest hit wanted: never stop early
-}
-
 // Per-lane traversal state (everything that lives across loop iterations).
 #define MP_LANE_STATE(F, I) \
-    F(0, r.ox) F(1, r.oy) F(2, r.oz) F(3, r.invX) F(4, r.invY) F(5, r.invZ) F(6, r.Sx) F(7, r.Sy) F(8, r.Sz) \
-    F(9, r.okx) F(10, r.oky) F(11, r.okz) I(12, r.kx) I(13, r.ky) I(14, r.kz) F(15, t_max) \
-    F(16, tn[0]) F(17, tn[1]) F(18, tn[2]) F(19, tn[3]) I(20, ch[0]) I(21, ch[1]) I(22, ch[2]) I(23, ch[3]) \
-    I(24, tsz) I(25, rem) I(26, leafmask) I(27, leaf) I(28, ntri) I(29, sp) I(30, ray) I(31, hit_i)
+    F(0, r.ox) F(1, r.oy) F(2, r.oz) F(3, r.invX) F(4, r.invY) F(5, r.invZ) I(6, r.offX) I(7, r.offY) I(8, r.offZ) \
+    F(9, t_max) F(10, tn[0]) F(11, tn[1]) F(12, tn[2]) F(13, tn[3]) I(14, nd) I(15, rem) I(16, leaf) \
+    I(17, sp) I(18, ray)
 #define MP_STASH_F(i, x) sv[i] = __float_as_int(x);
 #define MP_STASH_I(i, x) sv[i] = (int32_t)(x);
 #define MP_UNSTASH_F(i, x) x = __int_as_float(sv[i]);
 #define MP_UNSTASH_I(i, x) x = sv[i];
-constexpr int kLaneStateWords = 32;
+constexpr int kLaneStateWords = 19;
 
 // Tasks are handed out by a device-wide counter (warps that draw cheap tasks take more of
 // them); a warp numbers the tasks it draws 0, 1, ... and task seq lives in buffer seq & 1.  Warp-uniform stream state:
@@ -210,19 +196,19 @@ __global__ void __launch_bounds__(kStreamWarpsPerCTA * 32, MPENV_STREAM_MINB) k_
         }
     }
 
-    const unsigned lane_lt = (1u << (threadIdx.x & 31)) - 1u;
     int32_t stack[32 + kLaneStateWords];     // traversal stack + the stash used around a task change
     int32_t sp = 0;
     int32_t ray = -1;                // the lane's ray | buffer of its task << 8
     bool can_issue = true;
     RayRegs r;
-    float t_max = FLT_MAX;
-    int32_t hit_i = 0;               // the ray has an accepted hit
+    r.tStop = -1.f;                  // closest hit wanted: never stop early
+    float t_max = FLT_MAX;           // FLT_MAX = no accepted hit yet (no hit lies that far in a bounded map)
+    uint32_t nd = 0;                 // the current node (shared-memory offset)
     float tn[4] = {0.f, 0.f, 0.f, 0.f};
-    int32_t ch[4] = {0, 0, 0, 0};
-    uint32_t tsz = 0;
-    uint32_t rem = 0, leafmask = 0;
-    int32_t leaf = -1, ntri = 0;
+    uint32_t rem = 0;
+    int32_t leaf = -1;               // leaf waiting for its triangle tests: first triangle | count << 24
+    const char *smem = reinterpret_cast<const char *>(smem_raw);
+    const uint32_t trav_off = (uint32_t)(reinterpret_cast<const char *>(P.trav) - smem);
 
     for (;;) {
         const bool idle = leaf < 0 && rem == 0 && sp == 0;
@@ -234,7 +220,7 @@ __global__ void __launch_bounds__(kStreamWarpsPerCTA * 32, MPENV_STREAM_MINB) k_
             int32_t remaining0 = P.st[4], remaining1 = P.st[5];
             // retire finished rays
             const unsigned fresh1_m = __ballot_sync(0xFFFFFFFFu, idle && ray >= 256);
-            if (idle && ray >= 0) P.tmesh[ray >> 8][ray & 255] = hit_i ? t_max : -1.f;
+            if (idle && ray >= 0) P.tmesh[ray >> 8][ray & 255] = t_max != FLT_MAX ? t_max : -1.f;
             remaining1 -= __popc(fresh1_m);
             remaining0 -= __popc(fresh_m) - __popc(fresh1_m);
             if (idle) ray = -1;
@@ -270,15 +256,18 @@ __global__ void __launch_bounds__(kStreamWarpsPerCTA * 32, MPENV_STREAM_MINB) k_
             // end stay idle and are served from the next task on the next round
             if (iss < prep) {
                 if (idle) {
-                    const int32_t cand = next_ray + __popc(idle_m & lane_lt);
+                    const int32_t cand = next_ray + __popc(idle_m & ((1u << (threadIdx.x & 31)) - 1u));
                     if (cand < kLidarTaskRays) {
                         const int32_t b = iss & 1;
                         ray = cand | (b << 8);
                         int ag, rr, h, d;
                         lidarDecode(cand, &ag, &rr, &h, &d);
-                        setRayTrav(r, P.origin[b][ag * 2 + h], P.trav[b][d]);
+                        {
+                            const float4 o = P.origin[b][ag * 2 + h];
+                            const float4 tv = *reinterpret_cast<const float4 *>(&P.trav[b][d]);
+                            setRay(r, o.x, o.y, o.z, tv.x, tv.y, tv.z, 0);
+                        }
                         t_max = FLT_MAX;
-                        hit_i = 0;
                         stack[0] = 0;
                         sp = 1;
                     }
@@ -295,55 +284,28 @@ __global__ void __launch_bounds__(kStreamWarpsPerCTA * 32, MPENV_STREAM_MINB) k_
             __syncwarp();
         }
         if (leaf < 0 && rem == 0 && sp > 0) {
-            const int32_t node = stack[--sp];
-            const FastNode *nd = bvh.nodes + node;
-            const float4 h0 = reinterpret_cast<const float4 *>(nd)[0];    // minX minY minZ sX
-            const float4 h1 = reinterpret_cast<const float4 *>(nd)[1];    // sY sZ leafMask triSizes
-            const float dqx = h0.w * r.invX, dqy = h1.x * r.invY, dqz = h1.y * r.invZ;
-            const float oqx = (h0.x - r.ox) * r.invX;
-            const float oqy = (h0.y - r.oy) * r.invY;
-            const float oqz = (h0.z - r.oz) * r.invZ;
-            leafmask = __float_as_uint(h1.z);
-            tsz = __float_as_uint(h1.w);
-            rem = 0xFu;
-#pragma unroll
-            for (int i = 0; i < 4; i++) {
-                const FastChild k = nd->c[i];
-                tn[i] = childNear(k, dqx, dqy, dqz, oqx, oqy, oqz);
-                ch[i] = k.child;
-            }
-        }
-        if (leaf < 0 && rem != 0) {
-            uint32_t hits = 0;
-#pragma unroll
-            for (int i = 0; i < 4; i++) hits |= (tn[i] <= t_max ? 1u : 0u) << i;
-            hits &= rem;
-            const uint32_t leaf_hits = hits & leafmask;
-            const int32_t first_leaf = leaf_hits ? (__ffs(leaf_hits) - 1) : 4;
-            const uint32_t below = (1u << first_leaf) - 1u;
-            const uint32_t push = hits & ~leafmask & below;
-#pragma unroll
-            for (int i = 0; i < 4; i++) {
-                if ((push >> i) & 1u) stack[sp++] = ch[i];
-            }
-            if (first_leaf < 4) {
-                const int32_t cc = first_leaf == 0 ? ch[0] : first_leaf == 1 ? ch[1] : first_leaf == 2 ? ch[2] : ch[3];
-                leaf = cc & 0x7FFFFFFF;
-                ntri = (int32_t)((tsz >> (8 * first_leaf)) & 0xFFu);
-                rem &= ~(below | (1u << first_leaf));
+            nd = (uint32_t)stack[--sp] * (uint32_t)sizeof(FastNode);
+            if (r.offX >= 0) {
+                visitNode(smem + nd, r, ka.one, tn);
             } else {
-                rem = 0;
+                const float4 v = visitNodeRef(smem + nd, r.ox, r.oy, r.oz, r.invX, r.invY, r.invZ);
+                tn[0] = v.x; tn[1] = v.y; tn[2] = v.z; tn[3] = v.w;
             }
+            rem = 0xFu;
         }
+        if (leaf < 0 && rem != 0) leaf = walkChildren(smem + nd, tn, t_max, rem, stack, sp);
         const unsigned pend = __ballot_sync(0xFFFFFFFFu, leaf >= 0);
         const unsigned can_advance = __ballot_sync(0xFFFFFFFFu, leaf < 0 && (rem != 0 || sp > 0));
         if (leaf >= 0 && (__popc(pend) >= kLeafBatch || can_advance == 0)) {
-            for (int32_t k = 0; k < ntri; k++) {
+            int ag, rr, h, d;
+            lidarDecode(ray & 255, &ag, &rr, &h, &d);
+            r.tri = trav_off + (uint32_t)((ray >> 8) * 2 * kLidarDirsPerAgent + d) * (uint32_t)sizeof(RayTravRec) +
+                    (uint32_t)offsetof(RayTravRec, tri);
+            const TriConsts tc = loadTriConsts(smem, r);
+            const FastTri *tri = bvh.tris + (leaf & 0xFFFFFF);
+            for (int32_t k = 0; k < (leaf >> 24); k++) {
                 float t;
-                if (rayTriangleFast(bvh.tris + leaf + k, r, t_max, &t)) {
-                    hit_i = 1;
-                    t_max = t;
-                }
+                if (rayTriangleFast(tri + k, tc, t_max, &t)) t_max = t;
             }
             leaf = -1;
         }

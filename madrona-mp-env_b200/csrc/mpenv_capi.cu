@@ -30,10 +30,6 @@ struct mpenv_handle {
     int device = 0;
     int numSMs = 0;
     cudaStream_t stream = nullptr;
-    cudaStream_t sideStream = nullptr;       // capture-time fork of the obs phase
-    cudaEvent_t evFork = nullptr, evJoin = nullptr;
-    bool forkObs = false;                    // measured slower on B200 (3.17 vs 3.02 ms/step): the
-                                             // persistent lidar grid already fills every SM
     MapAssets assets;
     MapConsts hostConsts;
     MapConsts *devConsts = nullptr;
@@ -53,11 +49,9 @@ struct mpenv_handle {
     char *snapshot = nullptr;
     size_t snapshotBytes = 0;
     bool copyInFlight = false;
-    bool poolLidar = false;                  // warp-pooled ray engine (ray_kernels.cuh)
+    bool poolLidar = false;                  // warp-pooled ray engine (ray_fast.cuh): lidar task stream
     size_t lidarPoolSmem = 0;
     int gridLidarPool = 0;
-    int lidarBlock = kLidarWarpsPerCTA * 32;
-    void (*lidarPoolKernel)(KernelArgs) = nullptr;
     bool poolLos = false;
     size_t losPoolSmem = 0;
     int gridLosPool = 0;
@@ -118,7 +112,8 @@ int gridFor(mpenv_handle *h, K kernel, int block, size_t smem, long long items)
 
 void launchLidar(mpenv_handle *h, cudaStream_t s)
 {
-    if (h->poolLidar) h->lidarPoolKernel<<<h->gridLidarPool, h->lidarBlock, h->lidarPoolSmem, s>>>(h->ka);
+    if (h->poolLidar)
+        k_lidar_stream<MPENV_STREAM_LEAF, MPENV_STREAM_REFILL><<<h->gridLidarPool, kStreamWarpsPerCTA * 32, h->lidarPoolSmem, s>>>(h->ka);
     else k_lidar<<<h->gridLidar, 160, h->bvhSmemBytes, s>>>(h->ka);
 }
 
@@ -130,41 +125,19 @@ void launchLos(mpenv_handle *h, cudaStream_t s)
 
 // The obs phase shared by the Init and Step graphs (resetAndObsTasks,
 // sim.cpp:5174-5320): visibility -> masks + observations -> full-team -> lidar.
-uint32_t launchObsPhase(mpenv_handle *h, cudaStream_t s, bool fork)
+uint32_t launchObsPhase(mpenv_handle *h, cudaStream_t s)
 {
+    // One stream: lidar beside visibility -> observations on a forked graph branch was
+    // measured slower (3.17 vs 3.02 ms/step; the persistent lidar grid already fills every SM).
     uint32_t n = 0;
-    if (!fork) {
-        launchLos(h, s); n++;
-        k_obs<<<h->gridObs, 128, 0, s>>>(h->ka); n++;
-        if (h->fullTeam) { k_fullteam<<<h->gridTeam, 128, 0, s>>>(h->ka); n++; }
-        launchLidar(h, s); n++;
-        return n;
-    }
-    // Graph capture: the lidar kernel (issue bound, reads pos / aim / rot / stand only)
-    // runs beside visibility -> observation packing (latency / HBM bound).  With the
-    // full-team tensors the side branch starts after visibility, because
-    // k_fullteam reads canSee and must see the PREVIOUS step's lidar.
-    cudaStream_t side = h->sideStream;
-    if (!h->fullTeam) {
-        cudaEventRecord(h->evFork, s);
-        cudaStreamWaitEvent(side, h->evFork, 0);
-        launchLidar(h, side); n++;
-        launchLos(h, s); n++;
-        k_obs<<<h->gridObs, 128, 0, s>>>(h->ka); n++;
-    } else {
-        launchLos(h, s); n++;
-        cudaEventRecord(h->evFork, s);
-        cudaStreamWaitEvent(side, h->evFork, 0);
-        k_fullteam<<<h->gridTeam, 128, 0, side>>>(h->ka); n++;
-        launchLidar(h, side); n++;
-        k_obs<<<h->gridObs, 128, 0, s>>>(h->ka); n++;
-    }
-    cudaEventRecord(h->evJoin, side);
-    cudaStreamWaitEvent(s, h->evJoin, 0);
+    launchLos(h, s); n++;
+    k_obs<<<h->gridObs, 128, 0, s>>>(h->ka); n++;
+    if (h->fullTeam) { k_fullteam<<<h->gridTeam, 128, 0, s>>>(h->ka); n++; }
+    launchLidar(h, s); n++;
     return n;
 }
 
-uint32_t launchStep(mpenv_handle *h, cudaStream_t s, bool fork)
+uint32_t launchStep(mpenv_handle *h, cudaStream_t s)
 {
     uint32_t n = 0;
     if (!h->replayLog) {
@@ -185,7 +158,7 @@ uint32_t launchStep(mpenv_handle *h, cudaStream_t s, bool fork)
         k_event_scatter<<<h->gridSmall, 128, 0, s>>>(h->ka, h->devEvOffset, h->devSnapOffset, h->devEvOut,
                                                       h->devSnapOut); n++;
     }
-    n += launchObsPhase(h, s, fork);
+    n += launchObsPhase(h, s);
     return n;
 }
 
@@ -242,12 +215,12 @@ int logsAfterStep(mpenv_handle *h, cudaStream_t s)
     return MPENV_OK;
 }
 
-uint32_t launchInit(mpenv_handle *h, cudaStream_t s, bool fork)
+uint32_t launchInit(mpenv_handle *h, cudaStream_t s)
 {
     uint32_t n = 0;
     k_force_reset<<<h->gridSmall, 128, 0, s>>>(h->ka); n++;
     k_reset<<<h->gridSmall, 128, 0, s>>>(h->ka); n++;
-    n += launchObsPhase(h, s, fork);
+    n += launchObsPhase(h, s);
     return n;
 }
 
@@ -255,7 +228,7 @@ int captureGraph(mpenv_handle *h, bool step, cudaGraphExec_t *out, uint32_t *lau
 {
     cudaGraph_t graph = nullptr;
     MP_CUDA(h, cudaStreamBeginCapture(h->stream, cudaStreamCaptureModeThreadLocal));
-    *launches = step ? launchStep(h, h->stream, h->forkObs) : launchInit(h, h->stream, h->forkObs);
+    *launches = step ? launchStep(h, h->stream) : launchInit(h, h->stream);
     MP_CUDA(h, cudaStreamEndCapture(h->stream, &graph));
     MP_CUDA(h, cudaGraphInstantiate(out, graph, 0));
     MP_CUDA(h, cudaGraphDestroy(graph));
@@ -337,9 +310,6 @@ void mpenv_destroy(mpenv_handle *h)
     if (h->evSnap) cudaEventDestroy(h->evSnap);
     if (h->evCopied) cudaEventDestroy(h->evCopied);
     if (h->snapshot) cudaFree(h->snapshot);
-    if (h->evFork) cudaEventDestroy(h->evFork);
-    if (h->evJoin) cudaEventDestroy(h->evJoin);
-    if (h->sideStream) cudaStreamDestroy(h->sideStream);
     if (h->stream) cudaStreamDestroy(h->stream);
     delete h;
 }
@@ -395,10 +365,6 @@ int mpenv_create(const mpenv_config *cfg, mpenv_handle **out)
     MP_CREATE(cudaGetDeviceProperties(&prop, h->device));
     h->numSMs = prop.multiProcessorCount;
     MP_CREATE(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
-    MP_CREATE(cudaStreamCreateWithFlags(&h->sideStream, cudaStreamNonBlocking));
-    MP_CREATE(cudaEventCreateWithFlags(&h->evFork, cudaEventDisableTiming));
-    MP_CREATE(cudaEventCreateWithFlags(&h->evJoin, cudaEventDisableTiming));
-    { const char *f = getenv("MPENV_FORK_OBS"); h->forkObs = f && f[0] == '1'; }
 
     auto devAlloc = [&](void **ptr, size_t bytes) -> bool {
         if (!cudaOk(h, cudaMalloc(ptr, bytes), "cudaMalloc")) return false;
@@ -506,6 +472,7 @@ int mpenv_create(const mpenv_config *cfg, mpenv_handle **out)
     ka.ctx.bvh.rootAABB = h->assets.rootAABB;
     ka.ctx.bvh.numNodes = (uint32_t)h->assets.nodes.size();
     ka.ctx.bvh.numTris = h->assets.numTris;
+    ka.one = 1.0f;
     ka.bvhNodeWords = (uint32_t)(node_bytes / 4);
     ka.bvhVertWords = (uint32_t)(vert_bytes / 4);
     h->bvhSmemBytes = node_bytes + ((vert_bytes + 15) / 16) * 16;
@@ -538,11 +505,14 @@ int mpenv_create(const mpenv_config *cfg, mpenv_handle **out)
     h->gridLidar = gridFor(h, k_lidar, 160, h->bvhSmemBytes, N * 80);
     h->gridSmall = gridFor(h, k_reset, 128, 0, W);
 
-    // warp-pooled ray kernels: need the re-encoded BVH + per-warp pools in shared memory
+    // Warp-pooled ray kernels: need the re-encoded BVH + per-warp pools in shared memory.  A map
+    // whose BVH does not fit runs the per-thread k_los / k_lidar of step_kernels.cuh on the
+    // reference-format BVH (shared memory if that fits, else L2); MPENV_KERNELS=legacy forces
+    // that path so that the tests can cover it on simple_map.
     const char *kmode = getenv("MPENV_KERNELS");
     const bool legacy = kmode && strcmp(kmode, "legacy") == 0;
-    h->lidarPoolSmem = lidarPoolSmemBytes(ka.ctx.bvh.numNodes, ka.ctx.bvh.numTris);
-    h->poolLidar = !legacy && h->lidarPoolSmem <= 200 * 1024;
+    h->lidarPoolSmem = lidarStreamSmemBytes(ka.ctx.bvh.numNodes, ka.ctx.bvh.numTris);
+    h->poolLidar = !legacy && h->lidarPoolSmem <= 220 * 1024;
     h->losPoolSmem = losPoolSmemBytes(ka.ctx.bvh.numNodes, ka.ctx.bvh.numTris);
     h->poolLos = !legacy && h->losPoolSmem <= 200 * 1024;
     if (h->poolLos) {
@@ -550,24 +520,9 @@ int mpenv_create(const mpenv_config *cfg, mpenv_handle **out)
         h->gridLosPool = gridFor(h, k_los_pool<10, 8>, kLosWarpsPerCTA * 32, h->losPoolSmem, W * 32);
     }
     if (h->poolLidar) {
-        // leaf-batch threshold of the traversal loop (ray_fast.cuh); tunable for experiments
-        const char *lb = getenv("MPENV_LEAF_BATCH");
-        const int batch = lb ? atoi(lb) : kLeafBatch;
-        const char *rb = getenv("MPENV_REFILL_BATCH");
-        const int refill = rb ? atoi(rb) : kRefillBatch;
-        if (refill <= 1) h->lidarPoolKernel = batch <= 1 ? k_lidar_pool<1, 1> : k_lidar_pool<10, 1>;
-        else if (refill <= 4) h->lidarPoolKernel = batch <= 1 ? k_lidar_pool<1, 4> : k_lidar_pool<10, 4>;
-        else h->lidarPoolKernel = batch <= 1 ? k_lidar_pool<1, 8> : k_lidar_pool<10, 8>;
-        // default: the two-task stream (lidar_stream.cuh); MPENV_LIDAR=pool keeps one pool at a time
-        const char *lm = getenv("MPENV_LIDAR");
-        if (!(lm && strcmp(lm, "pool") == 0) && !lb && !rb) {
-            h->lidarPoolKernel = k_lidar_stream<MPENV_STREAM_LEAF, MPENV_STREAM_REFILL>;
-            h->lidarPoolSmem = lidarStreamSmemBytes(ka.ctx.bvh.numNodes, ka.ctx.bvh.numTris);
-            h->lidarBlock = kStreamWarpsPerCTA * 32;
-        }
-        MP_CREATE(cudaFuncSetAttribute(h->lidarPoolKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->lidarPoolSmem));
-        h->gridLidarPool = gridFor(h, h->lidarPoolKernel, h->lidarBlock, h->lidarPoolSmem,
-                                   (N / 2) * 32);
+        auto kern = k_lidar_stream<MPENV_STREAM_LEAF, MPENV_STREAM_REFILL>;
+        MP_CREATE(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->lidarPoolSmem));
+        h->gridLidarPool = gridFor(h, kern, kStreamWarpsPerCTA * 32, h->lidarPoolSmem, (N / 2) * 32);
     }
 
     // Sim::Sim for every world (sim.cpp:5850-5980)

@@ -24,25 +24,35 @@
 //    once per unique direction by converged lanes and parked in the pool.
 #pragma once
 
+#include <cstddef>
 #include <cuda_runtime.h>
 
 #include "mp_geom.h"
 
 namespace mpenv {
 
-struct FastChild {
-    float qMinX, qMinY, qMinZ, qMaxX, qMaxY, qMaxZ;
-    int32_t child;          // kBVHSentinel, leaf (bit 31) or node index
-    int32_t triSize;
-};
+// FastNode (240 bytes): header, children, then the quantised child bounds as
+// floats in (near, far) PAIRS, once per sign of the ray direction:
+//   b[axis][order][child] = order 0: (qMin, qMax)   order 1: (qMax, qMin)
+// A ray with a positive direction component enters a slab at qMin and leaves at
+// qMax (negative: the other way round), so the reference's
+//   fminf(t_near_x, t_far_x) / fmaxf(t_far_x, t_near_x)        (mesh_bvh.inl:168-171)
+// are picked by ADDRESS (b + 32 * order) instead of computed: q * dq + oq is
+// monotonic in q for a finite dq of known sign, so min/max of the two results is
+// the result of the min/max operand, bit for bit.  (dq is finite and non-zero for
+// every ray the engine accepts, see rayIsFast; others take the per-thread path.)
+// Each pair sits in an aligned register pair after one LDS.128 (two children), which
+// is the operand form of the packed FP32 instructions (FFMA2).
 struct __align__(16) FastNode {
-    float minX, minY, minZ, sX;
-    float sY, sZ;
-    uint32_t leafMask;      // bit i: child i is a leaf
-    uint32_t triSizes;      // triSize of child i in byte i
-    FastChild c[4];
+    float minX, minY, minZ;
+    uint32_t meta;          // bit i: child i is a leaf; bits 4 + 7 i .. : triSize of child i (<= kFastMaxTriSize)
+    float sX, sY, sZ;       // 2^exp of each axis
+    uint32_t pad;
+    int32_t child[4];       // kBVHSentinel, leaf (bit 31) or node index
+    float2 b[3][2][4];
 };
-static_assert(sizeof(FastNode) == 160, "FastNode is 10 x 16 bytes");
+constexpr uint32_t kFastMaxTriSize = 127;
+static_assert(sizeof(FastNode) == 240, "FastNode is 15 x 16 bytes");
 struct __align__(16) FastTri { float v[12]; };   // a.xyz b.xyz c.xyz + pad
 
 struct FastBVH {
@@ -63,30 +73,31 @@ __device__ __forceinline__ FastBVH stageFastBVH(const BVHView &g, void *smem)
     for (uint32_t i = threadIdx.x; i < g.numNodes * 4u; i += blockDim.x) {
         const uint32_t n = i >> 2, k = i & 3u;
         const BVHNode &src = g.nodes[n];
-        FastChild c;
-        c.qMinX = (float)src.qMinX[k]; c.qMinY = (float)src.qMinY[k]; c.qMinZ = (float)src.qMinZ[k];
-        c.qMaxX = (float)src.qMaxX[k]; c.qMaxY = (float)src.qMaxY[k]; c.qMaxZ = (float)src.qMaxZ[k];
-        c.child = src.children[k];
-        c.triSize = src.triSize[k];
+        float lo[3] = { (float)src.qMinX[k], (float)src.qMinY[k], (float)src.qMinZ[k] };
+        float hi[3] = { (float)src.qMaxX[k], (float)src.qMaxY[k], (float)src.qMaxZ[k] };
         if (src.children[k] == kBVHSentinel) {
             // absent child: NaN bounds make the slab test fail by itself (fminf / fmaxf drop the
             // NaN operand, so t_near = 0 and t_far = NaN, and 0 <= NaN is false) -- no sentinel
             // compare in the visit
             const float qnan = __int_as_float(0x7FC00000);
-            c.qMinX = c.qMinY = c.qMinZ = c.qMaxX = c.qMaxY = c.qMaxZ = qnan;
+            for (int ax = 0; ax < 3; ax++) lo[ax] = hi[ax] = qnan;
         }
-        sn[n].c[k] = c;
+        for (int ax = 0; ax < 3; ax++) {
+            sn[n].b[ax][0][k] = make_float2(lo[ax], hi[ax]);
+            sn[n].b[ax][1][k] = make_float2(hi[ax], lo[ax]);
+        }
+        sn[n].child[k] = src.children[k];
         if (k == 0) {
             sn[n].minX = src.minX; sn[n].minY = src.minY; sn[n].minZ = src.minZ;
             sn[n].sX = u2f((uint32_t)((int32_t)src.expX + 127) << 23);
             sn[n].sY = u2f((uint32_t)((int32_t)src.expY + 127) << 23);
             sn[n].sZ = u2f((uint32_t)((int32_t)src.expZ + 127) << 23);
-            uint32_t lm = 0, ts = 0;
+            uint32_t meta = 0;
             for (int q = 0; q < 4; q++) {
-                if (src.children[q] != kBVHSentinel && (src.children[q] & 0x80000000)) lm |= 1u << q;
-                ts |= (uint32_t)src.triSize[q] << (8 * q);
+                if (src.children[q] != kBVHSentinel && (src.children[q] & 0x80000000)) meta |= 1u << q;
+                meta |= ((uint32_t)src.triSize[q] & 0x7Fu) << (4 + 7 * q);
             }
-            sn[n].leafMask = lm; sn[n].triSizes = ts;
+            sn[n].meta = meta; sn[n].pad = 0;
         }
     }
     const float *gv = reinterpret_cast<const float *>(g.verts);
@@ -101,14 +112,21 @@ __device__ __forceinline__ FastBVH stageFastBVH(const BVHView &g, void *smem)
     return f;
 }
 
+// The triangle-test constants of a direction (Woop shear + axis permutation,
+// mesh_bvh.inl:584-741).  They stay in the pool: a lane keeps only the record's
+// shared-memory offset and fetches them when it has a leaf to test.
+struct __align__(16) RayTriRec {
+    float Sx, Sy, Sz;
+    int32_t kperm;               // kx | ky << 2 | kz << 4
+};
+
 // Per-direction constants parked in the pool (48 bytes).
 struct __align__(16) RayDirRec {
     float dx, dy, dz, invX;      // invX/Y/Z: the slab-test reciprocals (mesh_bvh.inl:125-135)
-    float invY, invZ, Sx, Sy;    // Woop shear (mesh_bvh.inl:584-741)
-    float Sz;
-    int32_t kperm;               // kx | ky << 2 | kz << 4
+    float invY, invZ;
     float a2;                    // dx*dx + dy*dy        (capsule side quadratic)
     float dd;                    // a2 + dz*dz           (capsule cap quadratic)
+    RayTriRec tri;
 };
 static_assert(sizeof(RayDirRec) == 48, "RayDirRec is 3 x 16 bytes");
 
@@ -122,22 +140,50 @@ __device__ __forceinline__ RayDirRec makeRayDirRec(Vec3 d)
     r.invX = copysignf(d.x == 0 ? 1 / diveps : 1 / d.x, d.x);
     r.invY = copysignf(d.y == 0 ? 1 / diveps : 1 / d.y, d.y);
     r.invZ = copysignf(d.z == 0 ? 1 / diveps : 1 / d.z, d.z);
-    r.Sx = tx.Sx; r.Sy = tx.Sy; r.Sz = tx.Sz;
-    r.kperm = tx.kx | (tx.ky << 2) | (tx.kz << 4);
+    r.tri.Sx = tx.Sx; r.tri.Sy = tx.Sy; r.tri.Sz = tx.Sz;
+    r.tri.kperm = tx.kx | (tx.ky << 2) | (tx.kz << 4);
     r.a2 = d.x * d.x + d.y * d.y;
     r.dd = r.a2 + d.z * d.z;
     return r;
 }
 
-// The ray a lane is currently traversing.
+// What a lane keeps in registers of the ray it is traversing: the node-visit part only.
+// Everything else (triangle constants, the node's children / leaf mask) is re-read from
+// shared memory at the few places that need it -- the traversal loop holds 28 warps per SM
+// at 72 registers.  Shared-memory objects are named by their byte offset from the CTA's
+// dynamic shared memory base (one register, and the loads stay LDS).
 struct RayRegs {
     float ox, oy, oz;
     float invX, invY, invZ;
-    float Sx, Sy, Sz;
-    float okx, oky, okz;         // origin permuted by (kx, ky, kz)
-    int32_t kx, ky, kz;
+    int32_t offX, offY, offZ;    // byte offset of the ray's (near, far) order within a FastNode
+    uint32_t tri;                // offset of its RayTriRec
     float tStop;                 // any-hit threshold: the ray ends at an accepted hit with t <= tStop
 };
+
+// Picking the reference's per-axis fminf / fmaxf by the sign of the direction needs finite
+// reciprocals whose products with the node scales and origins stay finite (no NaN from inf - inf
+// or 0 * inf, which fminf / fmaxf would drop): true for any direction component that is 0 (1e7 is
+// used, mesh_bvh.inl:125-135) or not absurdly small.  A ray that fails this (none does in practice:
+// directions are normalised) is marked offX < 0 and visits nodes with visitNodeRef.
+__device__ __forceinline__ bool rayIsFast(float invX, float invY, float invZ)
+{
+    return fabsf(invX) <= 1e30f && fabsf(invY) <= 1e30f && fabsf(invZ) <= 1e30f;
+}
+
+__device__ __forceinline__ void setRay(RayRegs &r, float ox, float oy, float oz, float invX, float invY,
+                                       float invZ, uint32_t tri_off)
+{
+    r.ox = ox; r.oy = oy; r.oz = oz;
+    r.invX = invX; r.invY = invY; r.invZ = invZ;
+    constexpr int kB = (int)offsetof(FastNode, b);
+    r.offX = !rayIsFast(invX, invY, invZ) ? -1 : kB + (invX < 0.f ? 32 : 0);
+#ifdef MPENV_FORCE_REF_VISIT
+    r.offX = -1;         // test builds: every ray through visitNodeRef
+#endif
+    r.offY = kB + 64 + (invY < 0.f ? 32 : 0);
+    r.offZ = kB + 128 + (invZ < 0.f ? 32 : 0);
+    r.tri = tri_off;
+}
 
 // x, y or z by index, as two SELs (a ?: chain compiles to divergent branches here).
 __device__ __forceinline__ float sel3(int32_t k, float x, float y, float z)
@@ -152,20 +198,28 @@ __device__ __forceinline__ float sel3(int32_t k, float x, float y, float z)
     return r;
 }
 
-__device__ __forceinline__ void setRay(RayRegs &r, float ox, float oy, float oz, const RayDirRec &d)
+// The per-leaf part of the triangle test: constants of the lane's ray, origin permuted.
+struct TriConsts {
+    float Sx, Sy, Sz;
+    float okx, oky, okz;
+    int32_t kx, ky, kz;
+};
+__device__ __forceinline__ TriConsts loadTriConsts(const char *smem, const RayRegs &r)
 {
-    r.ox = ox; r.oy = oy; r.oz = oz;
-    r.invX = d.invX; r.invY = d.invY; r.invZ = d.invZ;
-    r.Sx = d.Sx; r.Sy = d.Sy; r.Sz = d.Sz;
-    r.kx = d.kperm & 3; r.ky = (d.kperm >> 2) & 3; r.kz = (d.kperm >> 4) & 3;
-    r.okx = sel3(r.kx, ox, oy, oz);
-    r.oky = sel3(r.ky, ox, oy, oz);
-    r.okz = sel3(r.kz, ox, oy, oz);
+    const float4 v = *reinterpret_cast<const float4 *>(smem + r.tri);
+    const int32_t kperm = __float_as_int(v.w);
+    TriConsts c;
+    c.Sx = v.x; c.Sy = v.y; c.Sz = v.z;
+    c.kx = kperm & 3; c.ky = (kperm >> 2) & 3; c.kz = (kperm >> 4) & 3;
+    c.okx = sel3(c.kx, r.ox, r.oy, r.oz);
+    c.oky = sel3(c.ky, r.ox, r.oy, r.oz);
+    c.okz = sel3(c.kz, r.ox, r.oy, r.oz);
+    return c;
 }
 
 // rayTriangle of mp_geom.h (mesh_bvh.inl:433-554) on a FastTri; identical
 // arithmetic: comp(tri - org, k) == comp(tri, k) - comp(org, k).
-__device__ __forceinline__ bool rayTriangleFast(const FastTri *tri, const RayRegs &r, float t_max, float *out_t)
+__device__ __forceinline__ bool rayTriangleFast(const FastTri *tri, const TriConsts &r, float t_max, float *out_t)
 {
     // the permuted components come straight from shared memory by index (9 LDS.32) --
     // 3 LDS.128 + nine two-select sel3 chains cost 27 more issue slots per triangle
@@ -208,28 +262,157 @@ __device__ __forceinline__ bool rayTriangleFast(const FastTri *tri, const RayReg
     return true;
 }
 
-// One child's slab test against the visit-time constants (mesh_bvh.inl:146-177).
-// Returns t_near, or +inf when the child is absent or its box is missed.
-__device__ __forceinline__ float childNear(const FastChild &c, float dqx, float dqy, float dqz,
-                                           float oqx, float oqy, float oqz)
+// ---- packed FP32 (Blackwell FFMA2: two lanes of data per instruction) ------------
+// The slab test is  t = q * dq + oq  with two roundings (the reference is compiled without
+// contraction).  ptxas contracts mul.f32x2 + add.f32x2 into one FFMA2 whatever
+// the rounding qualifiers and -fmad say, so both steps are written as fma.rn.f32x2:
+//   p = fma(q, dq, -0)  == rn(q * dq)          (x + -0 == x for every x, signed zeros included)
+//   t = fma(p, ONE, oq) == rn(p + oq)          with ONE = 1.0f read from the kernel arguments,
+// a value ptxas cannot see, so it cannot fold the pair back into a single rounding.
+typedef unsigned long long f32x2;
+__device__ __forceinline__ f32x2 bcast2(float x)
 {
-    const float t_near_x = c.qMinX * dqx + oqx;
-    const float t_near_y = c.qMinY * dqy + oqy;
-    const float t_near_z = c.qMinZ * dqz + oqz;
-    const float t_far_x = c.qMaxX * dqx + oqx;
-    const float t_far_y = c.qMaxY * dqy + oqy;
-    const float t_far_z = c.qMaxZ * dqz + oqz;
-    const float t_near = fmaxf(fminf(t_near_x, t_far_x), fmaxf(fminf(t_near_y, t_far_y),
-        fmaxf(fminf(t_near_z, t_far_z), 0.f)));
-    const float t_far3 = fminf(fmaxf(t_far_x, t_near_x), fminf(fmaxf(t_far_y, t_near_y),
-        fmaxf(t_far_z, t_near_z)));
-    return t_near <= t_far3 ? t_near : __int_as_float(0x7F800000);      // absent children carry NaN bounds
+    f32x2 r;
+    asm("mov.b64 %0, {%1, %1};" : "=l"(r) : "f"(x));
+    return r;
+}
+__device__ __forceinline__ void unpack2(f32x2 v, float &lo, float &hi)
+{
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c)
+{
+    f32x2 d;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+    return d;
+}
+
+// One node visit (mesh_bvh.inl:142-177): t_near of the four children, +inf for a child that is
+// absent or whose box is missed without regard to t_max (the t_near <= t_max part of the
+// reference's test is taken at the child's turn, see traversePool).  `nd` = the node in
+// shared memory.
+__device__ __forceinline__ void visitNode(const char *nd, const RayRegs &r, float one, float tn[4])
+{
+    const float4 h0 = reinterpret_cast<const float4 *>(nd)[0];    // minX minY minZ meta
+    const float4 h1 = reinterpret_cast<const float4 *>(nd)[1];    // sX sY sZ -
+#ifndef MPENV_SCALAR_SLAB
+    const f32x2 dqx = bcast2(h1.x * r.invX), dqy = bcast2(h1.y * r.invY), dqz = bcast2(h1.z * r.invZ);
+    const f32x2 oqx = bcast2((h0.x - r.ox) * r.invX);
+    const f32x2 oqy = bcast2((h0.y - r.oy) * r.invY);
+    const f32x2 oqz = bcast2((h0.z - r.oz) * r.invZ);
+    const f32x2 one2 = bcast2(one), nz2 = 0x8000000080000000ull;
+#pragma unroll
+    for (int half = 0; half < 2; half++) {
+        const ulonglong2 qx = *reinterpret_cast<const ulonglong2 *>(nd + r.offX + 16 * half);
+        const ulonglong2 qy = *reinterpret_cast<const ulonglong2 *>(nd + r.offY + 16 * half);
+        const ulonglong2 qz = *reinterpret_cast<const ulonglong2 *>(nd + r.offZ + 16 * half);
+#pragma unroll
+        for (int k = 0; k < 2; k++) {
+            float nx, fx, ny, fy, nz, fz;
+            unpack2(fma2(fma2(k ? qx.y : qx.x, dqx, nz2), one2, oqx), nx, fx);
+            unpack2(fma2(fma2(k ? qy.y : qy.x, dqy, nz2), one2, oqy), ny, fy);
+            unpack2(fma2(fma2(k ? qz.y : qz.x, dqz, nz2), one2, oqz), nz, fz);
+            const float t_near = fmaxf(nx, fmaxf(ny, fmaxf(nz, 0.f)));
+            const float t_far3 = fminf(fx, fminf(fy, fz));
+            tn[2 * half + k] = t_near <= t_far3 ? t_near : __int_as_float(0x7F800000);
+        }
+    }
+#else
+    // scalar FMUL + FADD (measured: k_lidar 1.226 ms against 1.172 ms for the packed form)
+    (void)one;
+    const float dqx = h1.x * r.invX, dqy = h1.y * r.invY, dqz = h1.z * r.invZ;
+    const float oqx = (h0.x - r.ox) * r.invX;
+    const float oqy = (h0.y - r.oy) * r.invY;
+    const float oqz = (h0.z - r.oz) * r.invZ;
+#pragma unroll
+    for (int half = 0; half < 2; half++) {
+        const float4 qx = *reinterpret_cast<const float4 *>(nd + r.offX + 16 * half);   // near far | near far
+        const float4 qy = *reinterpret_cast<const float4 *>(nd + r.offY + 16 * half);
+        const float4 qz = *reinterpret_cast<const float4 *>(nd + r.offZ + 16 * half);
+#pragma unroll
+        for (int k = 0; k < 2; k++) {
+            const float nx = (k ? qx.z : qx.x) * dqx + oqx, fx = (k ? qx.w : qx.y) * dqx + oqx;
+            const float ny = (k ? qy.z : qy.x) * dqy + oqy, fy = (k ? qy.w : qy.y) * dqy + oqy;
+            const float nz = (k ? qz.z : qz.x) * dqz + oqz, fz = (k ? qz.w : qz.y) * dqz + oqz;
+            const float t_near = fmaxf(nx, fmaxf(ny, fmaxf(nz, 0.f)));
+            const float t_far3 = fminf(fx, fminf(fy, fz));
+            tn[2 * half + k] = t_near <= t_far3 ? t_near : __int_as_float(0x7F800000);
+        }
+    }
+#endif
+}
+
+// The same for a ray that fails rayIsFast: the reference's expressions with both bounds of every
+// axis computed and ordered by fminf / fmaxf (NaN operands dropped as the reference drops them).
+__device__ __noinline__ float4 visitNodeRef(const char *nd, float ox, float oy, float oz, float invX, float invY,
+                                           float invZ)
+{
+    float tn[4];
+    const float4 h0 = reinterpret_cast<const float4 *>(nd)[0];
+    const float4 h1 = reinterpret_cast<const float4 *>(nd)[1];
+    const float dqx = h1.x * invX, dqy = h1.y * invY, dqz = h1.z * invZ;
+    const float oqx = (h0.x - ox) * invX;
+    const float oqy = (h0.y - oy) * invY;
+    const float oqz = (h0.z - oz) * invZ;
+    const float2 *b = reinterpret_cast<const float2 *>(nd + offsetof(FastNode, b));      // [axis][order][child]
+    for (int i = 0; i < 4; i++) {
+        const float2 qx = b[0 * 8 + i], qy = b[1 * 8 + i], qz = b[2 * 8 + i];             // order 0: (qMin, qMax)
+        const float t_near_x = qx.x * dqx + oqx, t_far_x = qx.y * dqx + oqx;
+        const float t_near_y = qy.x * dqy + oqy, t_far_y = qy.y * dqy + oqy;
+        const float t_near_z = qz.x * dqz + oqz, t_far_z = qz.y * dqz + oqz;
+        const float t_near = fmaxf(fminf(t_near_x, t_far_x), fmaxf(fminf(t_near_y, t_far_y),
+            fmaxf(fminf(t_near_z, t_far_z), 0.f)));
+        const float t_far3 = fminf(fmaxf(t_far_x, t_near_x), fminf(fmaxf(t_far_y, t_near_y),
+            fmaxf(t_far_z, t_near_z)));
+        tn[i] = t_near <= t_far3 ? t_near : __int_as_float(0x7F800000);
+    }
+    return make_float4(tn[0], tn[1], tn[2], tn[3]);
+}
+
+// The in-order walk over the children of the lane's current node (mesh_bvh.inl:178-200) up to
+// the first leaf that needs testing; internal nodes are pushed.  t_near <= t_max is evaluated at
+// the child's turn, as the reference does: t_max is constant during one scan (only triangle tests
+// change it), so the four comparisons are taken at once and the walk becomes bit logic.
+// rem: slots still to consider.  Returns the leaf (first triangle index | triangle count << 24) or -1.
+__device__ __forceinline__ int32_t walkChildren(uint32_t meta, const int32_t child[4], const float tn[4], float t_max,
+                                                uint32_t &rem, int32_t *stack, int32_t &sp)
+{
+    const uint32_t leafmask = meta & 0xFu;
+    uint32_t hits = 0;
+#pragma unroll
+    for (int i = 0; i < 4; i++) hits |= (tn[i] <= t_max ? 1u : 0u) << i;
+    hits &= rem;
+    const uint32_t leaf_hits = hits & leafmask;
+    const int32_t first = leaf_hits ? (__ffs(leaf_hits) - 1) : 4;       // slot of the first leaf hit
+    const uint32_t below = (1u << first) - 1u;
+    const uint32_t push = hits & ~leafmask & below;
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+        if ((push >> i) & 1u) stack[sp++] = child[i];
+    }
+    if (first < 4) {
+        const int32_t ntri = (int32_t)((meta >> (4 + 7 * first)) & 0x7Fu);
+        rem &= ~(below | (1u << first));
+        return (child[first] & 0xFFFFFF) | (ntri << 24);
+    }
+    rem = 0;
+    return -1;
+}
+
+// The same with the node's meta word and children re-read from shared memory (for a loop that has
+// no registers to keep them in between the visit and a walk resumed after a leaf test).
+__device__ __forceinline__ int32_t walkChildren(const char *nd, const float tn[4], float t_max, uint32_t &rem,
+                                                int32_t *stack, int32_t &sp)
+{
+    return walkChildren(reinterpret_cast<const uint32_t *>(nd)[3], reinterpret_cast<const int32_t *>(nd + 32), tn,
+                        t_max, rem, stack, sp);
 }
 
 // Pool interface (duck-typed):
 //   int  count()                                 rays in this warp's pool
 //   void load(int ray, RayRegs &r)               fill the lane's registers
 //   void finish(int ray, bool hit, float t)      closest mesh hit of a finished ray
+// A ray that fails rayIsFast is traversed by the same loop with visitNodeRef instead of visitNode.
 //
 // Must be entered by all 32 lanes (warp-synchronous: ballots decide the batched
 // steps).  Two things are batched so that their code runs with many lanes
@@ -238,8 +421,9 @@ __device__ __forceinline__ float childNear(const FastChild &c, float dqx, float 
 //   * ray refill: a lane whose ray is finished parks until kRefillBatch lanes are
 //     idle; ray indices are handed out by ballot rank (no atomics).
 // Either fires at once when no other lane can make progress.
+// smem = the CTA's dynamic shared memory, which starts with the FastBVH.
 template <int kLeafBatch, int kRefillBatch, class Pool>
-__device__ __forceinline__ void traversePool(const FastBVH &bvh, Pool &pool)
+__device__ __forceinline__ void traversePool(const char *smem, const FastBVH &bvh, Pool &pool, float one)
 {
     const unsigned lane_lt = (1u << (threadIdx.x & 31)) - 1u;
     const int32_t pool_count = pool.count();
@@ -248,14 +432,15 @@ __device__ __forceinline__ void traversePool(const FastBVH &bvh, Pool &pool)
     int32_t sp = 0;
     int32_t ray = -1;
     RayRegs r;
-    float t_max = FLT_MAX;
-    bool hit = false, done = false;
-    // the current node: t_near / child / triSize per slot and the slots still to consider
-    float tn[4] = {0.f, 0.f, 0.f, 0.f};
+    float t_max = FLT_MAX;           // FLT_MAX = no accepted hit yet (no hit lies that far in a bounded map)
+    bool done = false;
+    // the current node: meta word, children, t_near per slot and the slots still to consider (kept
+    // in registers: the callers of this loop run at 80+ registers)
+    uint32_t meta = 0;
     int32_t ch[4] = {0, 0, 0, 0};
-    uint32_t tsz = 0;
-    uint32_t rem = 0, leafmask = 0;
-    int32_t leaf = -1, ntri = 0;
+    float tn[4] = {0.f, 0.f, 0.f, 0.f};
+    uint32_t rem = 0;
+    int32_t leaf = -1;               // leaf waiting for its triangle tests: first triangle | count << 24
 
     for (;;) {
         const bool idle = !done && leaf < 0 && rem == 0 && sp == 0;
@@ -265,12 +450,11 @@ __device__ __forceinline__ void traversePool(const FastBVH &bvh, Pool &pool)
         if ((idle_m | adv_m | pend_m) == 0) break;
         if (idle_m != 0 && (__popc(idle_m) >= kRefillBatch || adv_m == 0)) {
             if (idle) {
-                if (ray >= 0) pool.finish(ray, hit, t_max);
+                if (ray >= 0) pool.finish(ray, t_max != FLT_MAX, t_max);
                 ray = next_ray + __popc(idle_m & lane_lt);
                 if (ray < pool_count) {
                     pool.load(ray, r);
                     t_max = FLT_MAX;
-                    hit = false;
                     stack[0] = 0;
                     sp = 1;
                 } else {
@@ -281,64 +465,32 @@ __device__ __forceinline__ void traversePool(const FastBVH &bvh, Pool &pool)
             next_ray += __popc(idle_m);
         }
         if (!done && leaf < 0 && rem == 0 && sp > 0) {
-            const int32_t node = stack[--sp];
-            const FastNode *nd = bvh.nodes + node;
-            const float4 h0 = reinterpret_cast<const float4 *>(nd)[0];    // minX minY minZ sX
-            const float4 h1 = reinterpret_cast<const float4 *>(nd)[1];    // sY sZ leafMask triSizes
-            const float dqx = h0.w * r.invX, dqy = h1.x * r.invY, dqz = h1.y * r.invZ;
-            const float oqx = (h0.x - r.ox) * r.invX;
-            const float oqy = (h0.y - r.oy) * r.invY;
-            const float oqz = (h0.z - r.oz) * r.invZ;
-            leafmask = __float_as_uint(h1.z);
-            tsz = __float_as_uint(h1.w);
-            rem = 0xFu;                  // absent / missed children carry t_near = +inf
-#pragma unroll
-            for (int i = 0; i < 4; i++) {
-                const FastChild k = nd->c[i];
-                tn[i] = childNear(k, dqx, dqy, dqz, oqx, oqy, oqz);
-                ch[i] = k.child;
-            }
-        }
-        // Children in order until a leaf needs testing; internal nodes are pushed.
-        // t_near <= t_max is evaluated at the child's turn, as the reference does:
-        // t_max is constant during one scan (only triangle tests change it), so the
-        // four comparisons are taken at once and the in-order walk becomes bit logic.
-        if (leaf < 0 && rem != 0) {
-            uint32_t hits = 0;
-#pragma unroll
-            for (int i = 0; i < 4; i++) hits |= (tn[i] <= t_max ? 1u : 0u) << i;
-            hits &= rem;
-            const uint32_t leaf_hits = hits & leafmask;
-            const int32_t first = leaf_hits ? (__ffs(leaf_hits) - 1) : 4;       // slot of the first leaf hit
-            const uint32_t below = (1u << first) - 1u;
-            const uint32_t push = hits & ~leafmask & below;
-#pragma unroll
-            for (int i = 0; i < 4; i++) {
-                if ((push >> i) & 1u) stack[sp++] = ch[i];
-            }
-            if (first < 4) {
-                const int32_t c = first == 0 ? ch[0] : first == 1 ? ch[1] : first == 2 ? ch[2] : ch[3];
-                leaf = c & 0x7FFFFFFF;
-                ntri = (int32_t)((tsz >> (8 * first)) & 0xFFu);
-                rem &= ~(below | (1u << first));
+            const char *nd = smem + (uint32_t)stack[--sp] * (uint32_t)sizeof(FastNode);
+            if (r.offX >= 0) {
+                visitNode(nd, r, one, tn);
             } else {
-                rem = 0;
+                const float4 v = visitNodeRef(nd, r.ox, r.oy, r.oz, r.invX, r.invY, r.invZ);
+                tn[0] = v.x; tn[1] = v.y; tn[2] = v.z; tn[3] = v.w;
             }
+            meta = reinterpret_cast<const uint32_t *>(nd)[3];
+            const int4 cc = reinterpret_cast<const int4 *>(nd)[2];
+            ch[0] = cc.x; ch[1] = cc.y; ch[2] = cc.z; ch[3] = cc.w;
+            rem = 0xFu;                  // absent / missed children carry t_near = +inf
         }
+        if (leaf < 0 && rem != 0) leaf = walkChildren(meta, ch, tn, t_max, rem, stack, sp);
         const unsigned pend = __ballot_sync(0xFFFFFFFFu, leaf >= 0);
         const unsigned can_advance = __ballot_sync(0xFFFFFFFFu, !done && leaf < 0 && (rem != 0 || sp > 0));
         if (leaf >= 0 && (__popc(pend) >= kLeafBatch || can_advance == 0)) {
             // traceRayLeaf (mesh_bvh.inl:360-431): a later triangle replaces an
             // earlier one whenever T <= t_cur * det.
-            for (int32_t k = 0; k < ntri; k++) {
+            const TriConsts tc = loadTriConsts(smem, r);
+            const FastTri *tri = bvh.tris + (leaf & 0xFFFFFF);
+            for (int32_t k = 0; k < (leaf >> 24); k++) {
                 float t;
-                if (rayTriangleFast(bvh.tris + leaf + k, r, t_max, &t)) {
-                    hit = true;
-                    t_max = t;
-                }
+                if (rayTriangleFast(tri + k, tc, t_max, &t)) t_max = t;
             }
             leaf = -1;
-            if (hit && t_max <= r.tStop) { sp = 0; rem = 0; }     // occluder found: this ray is done
+            if (t_max <= r.tStop) { sp = 0; rem = 0; }     // occluder found: this ray is done
         }
     }
 }

@@ -31,6 +31,7 @@ struct KernelArgs {
     uint32_t bvhVertWords;   // 32-bit words of vertex data (incl. the pad triangle)
     int32_t bvhInSmem;       // 1: stage into shared memory, 0: traverse from global / L2
     uint32_t *workCounters;  // device-wide task counters of the dynamically scheduled kernels (zero between launches)
+    float one;               // 1.0f, opaque to ptxas: keeps the two roundings of q * dq + oq apart (ray_fast.cuh)
 };
 
 // ---- dynamic task hand-out --------------------------------------------------

@@ -8,6 +8,7 @@ Nothing here is imported by the product package.
 import ctypes as C
 import os
 import subprocess
+import sys
 
 import numpy as np
 
@@ -16,61 +17,17 @@ SCENE = os.path.join(ROOT, "data", "simple_map")
 ORACLE_DIR = os.path.join(ROOT, "oracle")
 REF_SO = os.path.join(ORACLE_DIR, "_ref", "libmpenv_ref.so")
 REF_DET_SO = os.path.join(ORACLE_DIR, "_ref", "libmpenv_ref_det.so")
+REF_FAST_SO = os.path.join(ORACLE_DIR, "_ref", "libmpenv_ref_fast.so")    # -O3 build of REF_SO: the timed CPU baseline
 DET_MATH_SO = os.path.join(ORACLE_DIR, "_ref", "libdet_math.so")
 HOSTSIM_SO = os.path.join(ROOT, "tests", "hostsim", "_build", "libhostsim.so")
 PRODUCT_SO = os.path.join(ROOT, "madrona-mp-env_b200", "libmpenv_b200.so")
 CSRC = os.path.join(ROOT, "madrona-mp-env_b200", "csrc")
+sys.path.insert(0, os.path.join(ROOT, "madrona-mp-env_b200"))
 
 AGENTS = 12
 
-# reference ExportID (src/sim.hpp:15-66)
-EXPORT_IDS = dict(
-    reset=0, world_curriculum=1, explore_action=2, pvp_discrete_action=3, pvp_aim_action=4,
-    pvp_discrete_aim_action=5, reward=6, done=7, match_result=8, agent_policy=9,
-    self_obs=10, teammate_obs=11, opponent_obs=12, opponent_last_known_obs=13,
-    self_pos=14, teammate_pos=15, opponent_pos=16, opponent_last_known_pos=17,
-    opponent_masks=18, fwd_lidar=19, rear_lidar=20, agent_map=21, unmasked_agent_map=22,
-    hp=23, alive=24, magazine=25, full_team_actions=26, full_team_global=27,
-    full_team_players=28, full_team_enemies=29, full_team_last_known_enemies=30,
-    full_team_fwd_lidar=31, full_team_rear_lidar=32, full_team_reward=33, full_team_done=34,
-    full_team_policy=35, event_log=36, packed_step_snapshot=37, filters_state_obs=38,
-    reward_hyper_params=39,
-)
-# per-row float/int32 counts and dtype; rows: 'agent' (W*12), 'world' (W), 'team' (W*2)
-EXPORT_SHAPES = dict(
-    reset=("world", 1, np.int32), world_curriculum=("world", 1, np.int32),
-    pvp_discrete_action=("agent", 4, np.int32), pvp_aim_action=("agent", 2, np.float32),
-    pvp_discrete_aim_action=("agent", 2, np.int32), reward=("agent", 1, np.float32),
-    done=("agent", 1, np.int32), match_result=("world", 30, np.int32),
-    agent_policy=("agent", 1, np.int32), self_obs=("agent", 43, np.float32),
-    teammate_obs=("agent", 5 * 32, np.float32), opponent_obs=("agent", 6 * 32, np.float32),
-    opponent_last_known_obs=("agent", 6 * 32, np.float32), self_pos=("agent", 3, np.float32),
-    teammate_pos=("agent", 15, np.float32), opponent_pos=("agent", 18, np.float32),
-    opponent_last_known_pos=("agent", 18, np.float32), opponent_masks=("agent", 6, np.float32),
-    fwd_lidar=("agent", 2 * 32 * 4, np.float32), rear_lidar=("agent", 2 * 8 * 4, np.float32),
-    hp=("agent", 1, np.float32), alive=("agent", 1, np.float32), magazine=("agent", 2, np.int32),
-    full_team_global=("team", 16, np.float32), full_team_players=("team", 6 * 28, np.float32),
-    full_team_enemies=("team", 6 * 33, np.float32),
-    full_team_last_known_enemies=("team", 6 * 24, np.float32),
-    full_team_fwd_lidar=("team", 6 * 256, np.float32), full_team_rear_lidar=("team", 6 * 64, np.float32),
-    full_team_reward=("team", 1, np.float32), full_team_done=("team", 1, np.int32),
-    filters_state_obs=("agent", 1, np.float32), reward_hyper_params=("agent", 9, np.float32),
-)
-# the train-interface outputs (mgr.cpp:2398-2431) + exported state
-STEP_OUTPUTS = [
-    "self_obs", "teammate_obs", "opponent_obs", "opponent_last_known_obs", "self_pos",
-    "teammate_pos", "opponent_pos", "opponent_last_known_pos", "opponent_masks", "fwd_lidar",
-    "rear_lidar", "hp", "alive", "magazine", "filters_state_obs", "reward", "done", "match_result",
-    "reward_hyper_params",
-]
-FULL_TEAM_OUTPUTS = [
-    "full_team_global", "full_team_players", "full_team_enemies", "full_team_last_known_enemies",
-    "full_team_fwd_lidar", "full_team_rear_lidar", "full_team_reward", "full_team_done",
-]
-
-
-def rows_of(kind, num_worlds):
-    return {"agent": num_worlds * AGENTS, "world": num_worlds, "team": num_worlds * 2}[kind]
+from madrona_mp_env.exports import (EXPORT_IDS, EXPORT_SHAPES, STEP_OUTPUTS, FULL_TEAM_OUTPUTS,  # noqa: E402,F401
+                                     rows_of)
 
 
 # ---------------------------------------------------------------- world state
@@ -209,12 +166,12 @@ def build_hostsim():
 def build_oracle():
     """Builds oracle/_ref/*.so when /root/reference is present (this container);
     on the GPU box the prebuilt files travel with the snapshot."""
-    have = all(os.path.exists(p) for p in (REF_SO, REF_DET_SO, DET_MATH_SO))
+    have = all(os.path.exists(p) for p in (REF_SO, REF_DET_SO, REF_FAST_SO, DET_MATH_SO))
     if os.path.isdir("/root/reference/src"):
         deps = [os.path.join(ORACLE_DIR, f) for f in ("ref_driver.cpp", "det_math_override.h",
                 "det_math_probe.cpp", "shim/shim_core.cpp", "shim/madrona/shim_core.hpp",
                 "shim/madrona/geo.hpp", "Makefile")] + [os.path.join(CSRC, "mp_math.h")]
-        if not have or any(_stale(p, deps) for p in (REF_SO, REF_DET_SO, DET_MATH_SO)):
+        if not have or any(_stale(p, deps) for p in (REF_SO, REF_DET_SO, REF_FAST_SO, DET_MATH_SO)):
             _run(["make", "-j4"], cwd=ORACLE_DIR)
     elif not have:
         raise RuntimeError("oracle/_ref is missing and /root/reference is not available to build it")
@@ -381,9 +338,12 @@ class Oracle(_SimBase):
 
     def __init__(self, num_worlds, rand_seed=10, auto_reset=False, sim_flags=0, det=True,
                  world_id_offset=0, num_threads=1, scene=SCENE, bvh=None, event_log=False,
-                 record_log=False, replay_log=False, curriculum=None, navmesh=True, train_flank=False):
+                 record_log=False, replay_log=False, curriculum=None, navmesh=True, train_flank=False,
+                 fast=False):
+        """fast=True (with det=False): the -O3 build of the libm oracle, for timing only."""
         build_oracle()
-        self.lib = C.CDLL(REF_DET_SO if det else REF_SO)
+        assert not (fast and det), "the timed -O3 build exists for the libm arithmetic only"
+        self.lib = C.CDLL(REF_DET_SO if det else (REF_FAST_SO if fast else REF_SO))
         L = self.lib
         L.ref_create.restype = C.c_void_p
         L.ref_create.argtypes = [C.POINTER(RefConfig), C.c_char_p, C.c_void_p, C.c_uint32,

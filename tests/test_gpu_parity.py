@@ -307,29 +307,42 @@ def test_pipelined_readback_equals_sync_read():
 
 
 @pytest.mark.parametrize("W", [1, 3, 37, 700])
-def test_lidar_stream_equals_single_pool(W, monkeypatch):
-    """k_lidar_stream (two resident tasks per warp, lidar_stream.cuh) against k_lidar_pool (one
-    160-ray pool at a time) and, at the small sizes, the oracle: warps with no task, one task,
-    an odd number of tasks and a long stream of them."""
-    monkeypatch.setenv("MPENV_LIDAR", "pool")
-    pool = S.GpuSim(W, auto_reset=True)
-    monkeypatch.delenv("MPENV_LIDAR")
-    stream = S.GpuSim(W, auto_reset=True)
-    orc = S.Oracle(W, auto_reset=True, det=True) if W <= 37 else None
-    sims = [s for s in (pool, stream, orc) if s is not None]
+def test_lidar_stream_vs_oracle(W):
+    """k_lidar_stream (two resident tasks per warp, tasks drawn from a device-wide counter,
+    lidar_stream.cuh) against the oracle: warps with no task, one task, an odd number of
+    tasks and a long stream of them."""
+    gpu = S.GpuSim(W, auto_reset=True, full_team=False)
+    orc = S.Oracle(W, auto_reset=True, det=True, num_threads=0)
     try:
-        for s in sims:
-            s.init()
-        for step in range(40):
+        gpu.init(); orc.init()
+        for step in range(40 if W <= 37 else 12):
             d, a = S.random_actions(step, W)
-            for s in sims:
+            for s in (gpu, orc):
                 s.set_actions(d, a)
                 s.step()
             for name in ("fwd_lidar", "rear_lidar"):
-                x = stream.export(name).view(np.int32)
-                assert np.array_equal(x, pool.export(name).view(np.int32)), f"step {step}: {name} stream vs pool"
-                if orc is not None:
-                    assert np.array_equal(x, orc.export(name).view(np.int32)), f"step {step}: {name} vs oracle"
+                assert np.array_equal(gpu.export(name).view(np.int32), orc.export(name).view(np.int32)), \
+                    f"step {step}: {name}"
     finally:
-        for s in sims:
-            s.close()
+        gpu.close(); orc.close()
+
+
+def test_large_map_fallback_kernels(monkeypatch):
+    """MPENV_KERNELS=legacy: the per-thread k_los / k_lidar of step_kernels.cuh on the
+    reference-format BVH -- the path mpenv_create takes by itself for a map whose BVH does
+    not fit in shared memory (mpenv_capi.cu) -- against the oracle."""
+    monkeypatch.setenv("MPENV_KERNELS", "legacy")
+    W = 8
+    gpu = S.GpuSim(W, auto_reset=True)
+    monkeypatch.delenv("MPENV_KERNELS")
+    orc = S.Oracle(W, auto_reset=True, det=True, num_threads=0)
+    try:
+        gpu.init(); orc.init()
+        for s in range(120):
+            d, a = S.seek_policy(orc, s, W)
+            for sim in (gpu, orc):
+                sim.set_actions(d, a); sim.step()
+            if s % 10 == 9:
+                assert_same(gpu, orc, W, f"legacy step {s}")
+    finally:
+        gpu.close(); orc.close()
