@@ -555,8 +555,23 @@ __device__ __forceinline__ float rayCapsuleRec(const CapsuleRec &c, float dx, fl
     return t_hit == FLT_MAX ? 0.f : t_hit;
 }
 
+// Conservative reject in front of rayCapsuleRec: a ray whose horizontal projection passes the
+// capsule's axis at more than r + 2 cannot touch the capsule -- all three discriminants are
+// negative, so rayCapsuleRec would return 0 ("no hit").  |cross| / sqrt(a2) is that distance;
+// the sphere caps' 3-D distance to the ray is at least as large.  Margin: at the cull radius the
+// true discriminants are <= -64 a2 (-64 dd for the caps) while their rounding error is < 12 a2
+// for any origin inside a 5,700-unit world (6e-8 * 6 * |o|^2), so no touching ray is rejected.
+// (ox, oy): ray origin relative to the capsule, as CapsuleRec holds it.
+constexpr float kCapsuleCullR2 = (kAgentRadius + 2.f) * (kAgentRadius + 2.f);
+__device__ __forceinline__ bool capsuleMayHit(float ox, float oy, float dx, float dy, float a2)
+{
+    const float cr = oy * dx - ox * dy;
+    return !(cr * cr > kCapsuleCullR2 * a2);
+}
+
 // The capsule half of traceRayWorld (utils.cpp:39-61): starts from the mesh
-// result and returns the closest hit over the 12 agents of the world.
+// result and returns the closest hit over the 12 agents of the world.  The agents are
+// visited in index order (an earlier agent keeps a tie), skipping those capsuleMayHit rules out.
 __device__ __forceinline__ bool closestWithCapsules(const CapsuleRec *caps, bool mesh_hit, float mesh_t,
                                                     float dx, float dy, float dz, float a2, float dd,
                                                     float *t_out, int32_t *agent_out)
@@ -564,8 +579,15 @@ __device__ __forceinline__ bool closestWithCapsules(const CapsuleRec *caps, bool
     float min_hit_t = mesh_hit ? mesh_t : FLT_MAX;
     bool hit = mesh_hit;
     int32_t hit_agent = -1;
+    uint32_t cand = 0;
 #pragma unroll
     for (int i = 0; i < kAgents; i++) {
+        const float2 oxy = *reinterpret_cast<const float2 *>(&caps[i]);
+        cand |= capsuleMayHit(oxy.x, oxy.y, dx, dy, a2) ? 1u << i : 0u;
+    }
+    while (cand) {
+        const int i = __ffs(cand) - 1;
+        cand &= cand - 1u;
         const float t = rayCapsuleRec(caps[i], dx, dy, dz, a2, dd);
         if (t != 0 && t < min_hit_t) {
             min_hit_t = t;

@@ -40,7 +40,10 @@ __device__ __forceinline__ void lidarDecode(int ray, int *agent, int *rr, int *h
 // stops at the first ACCEPTED mesh hit with t <= t_target -- accepted hits only
 // decrease, so such a hit exists iff the final closest mesh hit is <= t_target.
 // canSee[pair] = OR of its four samples (pure per sample, order irrelevant).
-constexpr int kLosWarpsPerCTA = 8;
+#ifndef MPENV_LOS_WARPS
+#define MPENV_LOS_WARPS 24      // one CTA per SM: the re-encoded BVH (27 KB on simple_map) is staged once, 24 x 6.6 KB of pools
+#endif
+constexpr int kLosWarpsPerCTA = MPENV_LOS_WARPS;
 constexpr int kLosPoolCap = 96;
 constexpr int kLosCandidates = kAgents * kTeamSize * 4;      // 288
 
@@ -76,7 +79,7 @@ struct LosPoolAccess {
 
 template <int kBatch, int kRefill>
 #ifndef MPENV_LOS_MINB
-#define MPENV_LOS_MINB 3        // 80 registers, no spills; 24 warps / SM: 0.200 -> 0.177 ms
+#define MPENV_LOS_MINB 1        // 24 warps at <= 80 registers
 #endif
 __global__ void __launch_bounds__(kLosWarpsPerCTA * 32, MPENV_LOS_MINB) k_los_pool(KernelArgs ka)
 {
@@ -166,6 +169,7 @@ __global__ void __launch_bounds__(kLosWarpsPerCTA * 32, MPENV_LOS_MINB) k_los_po
                     for (int i = 0; i < kAgents && ok; i++) {
                         if (i == opp) continue;
                         const float4 t4 = P.target[i];
+                        if (!capsuleMayHit(o4.x - t4.x, o4.y - t4.y, dir.x, dir.y, a2)) continue;   // t would be 0
                         const float t = rayCapsuleRec(makeCapsuleRec(v3(o4.x, o4.y, o4.z), v3(t4.x, t4.y, t4.z)),
                                                       dir.x, dir.y, dir.z, a2, dd);
                         if (t != 0.f && (i < opp ? !(t_tgt < t) : (t < t_tgt))) ok = false;
