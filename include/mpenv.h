@@ -15,6 +15,7 @@
 #ifndef MPENV_H
 #define MPENV_H
 
+#include <stddef.h>
 #include <stdint.h>
 #include "mpenv_state.h"
 
@@ -144,6 +145,18 @@ int mpenv_step_async(mpenv_handle *h, void *cuda_stream);
  * outputs back, all on `cuda_stream`.  Buffer order = mpenv_train_interface(). */
 int mpenv_stream_init(mpenv_handle *h, void *cuda_stream, void **buffers);
 int mpenv_stream_step(mpenv_handle *h, void *cuda_stream, void **buffers);
+/* Debug aid (no reference counterpart): every device buffer of the handle is allocated between two
+ * 256-byte guard bands; this counts the buffers whose bands were written to (0 = no kernel wrote
+ * out of bounds since mpenv_create).  Synchronises the handle's stream. */
+int mpenv_check_guards(mpenv_handle *h, uint32_t *num_damaged);
+/* XLA GPU custom-call entry points for sim.jax() (bindings.cpp:149-158: madrona::py::JAXInterface
+ * registers gpuStreamInit / gpuStreamStep as XLA custom calls).  Signature = XLA's original GPU
+ * custom-call ABI, void(cudaStream_t, void **buffers, const char *opaque, size_t opaque_len);
+ * `opaque` carries the 8 bytes of the mpenv_handle pointer (as the reference packs its Manager *),
+ * `buffers` = the train-interface inputs then outputs, mpenv_train_interface() order.  They forward
+ * to mpenv_stream_init / mpenv_stream_step; an error is printed and left in mpenv_last_error(). */
+void mpenv_xla_init(void *cuda_stream, void **buffers, const char *opaque, size_t opaque_len);
+void mpenv_xla_step(void *cuda_stream, void **buffers, const char *opaque, size_t opaque_len);
 /* The handle's own cudaStream_t (the stream of mpenv_step / the *_tensor_async copies). */
 void *mpenv_stream(mpenv_handle *h);
 /* Waits for the handle's own stream. */

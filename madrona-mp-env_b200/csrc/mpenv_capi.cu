@@ -9,6 +9,8 @@
 
 #include <cstdlib>
 
+#include <nvtx3/nvToolsExt.h>
+
 #include "step_kernels.cuh"
 #include "lidar_stream.cuh"
 #include "assets.h"
@@ -37,6 +39,8 @@ struct mpenv_handle {
     Vec3 *devVerts = nullptr;
     KernelArgs ka;
     std::vector<void *> allocs;
+    struct Guarded { char *raw; size_t bytes; };
+    std::vector<Guarded> guarded;            // buffers between guard bands (mpenv_check_guards)
     float *agentMap = nullptr;               // [N,16,16,4] zeros (never written, mgr.cpp:2422)
     unsigned long long *devStats = nullptr;
     size_t bvhSmemBytes = 0;
@@ -77,7 +81,15 @@ struct mpenv_handle {
     bool replayPending = false;              // mpenv_set_replay_log() data waiting for the next step
 };
 
+constexpr size_t kGuardBytes = 256;
+
 namespace {
+
+// NVTX range over a host-side entry point (nsys / ncu timelines; a no-op without a profiler attached).
+struct NvtxRange {
+    explicit NvtxRange(const char *name) { nvtxRangePushA(name); }
+    ~NvtxRange() { nvtxRangePop(); }
+};
 
 bool cudaOk(mpenv_handle *h, cudaError_t e, const char *what)
 {
@@ -316,6 +328,7 @@ void mpenv_destroy(mpenv_handle *h)
 
 int mpenv_create(const mpenv_config *cfg, mpenv_handle **out)
 {
+    NvtxRange nvtx("mpenv_create");
     if (!cfg || !out || !cfg->scene_dir) return fail(nullptr, MPENV_ERR_INVALID, "null argument");
     if (cfg->task_type != MPENV_TASK_ZONE) return fail(nullptr, MPENV_ERR_INVALID, "only Task::Zone is implemented");
     if (cfg->team_size != (uint32_t)kTeamSize) return fail(nullptr, MPENV_ERR_INVALID, "team_size must be 6");
@@ -366,10 +379,18 @@ int mpenv_create(const mpenv_config *cfg, mpenv_handle **out)
     h->numSMs = prop.multiProcessorCount;
     MP_CREATE(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
 
+    // Every device buffer sits between two 256-byte guard bands filled with 0xA5
+    // (mpenv_check_guards): compute-sanitizer is not available on every pool, the bands catch an
+    // out-of-bounds write of any kernel at the cost of 512 bytes per buffer.
     auto devAlloc = [&](void **ptr, size_t bytes) -> bool {
-        if (!cudaOk(h, cudaMalloc(ptr, bytes), "cudaMalloc")) return false;
-        h->allocs.push_back(*ptr);
-        return cudaOk(h, cudaMemsetAsync(*ptr, 0, bytes, h->stream), "cudaMemsetAsync");
+        char *raw = nullptr;
+        const size_t padded = (bytes + 255) & ~(size_t)255;
+        if (!cudaOk(h, cudaMalloc((void **)&raw, padded + 2 * kGuardBytes), "cudaMalloc")) return false;
+        h->allocs.push_back(raw);
+        h->guarded.push_back({raw, bytes});
+        *ptr = raw + kGuardBytes;
+        return cudaOk(h, cudaMemsetAsync(raw, 0xA5, padded + 2 * kGuardBytes, h->stream), "cudaMemsetAsync") &&
+               cudaOk(h, cudaMemsetAsync(*ptr, 0, bytes, h->stream), "cudaMemsetAsync");
     };
 
     // static assets
@@ -541,6 +562,7 @@ int mpenv_create(const mpenv_config *cfg, mpenv_handle **out)
 int mpenv_init_async(mpenv_handle *h, void *cuda_stream)
 {
     if (!h) return MPENV_ERR_INVALID;
+    NvtxRange nvtx("mpenv_init (Init graph: reset -> visibility -> observations -> lidar)");
     MP_CUDA(h, cudaSetDevice(h->device));
     MP_CUDA(h, cudaGraphLaunch(h->initGraph, (cudaStream_t)cuda_stream));
     return MPENV_OK;
@@ -549,6 +571,7 @@ int mpenv_init_async(mpenv_handle *h, void *cuda_stream)
 int mpenv_step_async(mpenv_handle *h, void *cuda_stream)
 {
     if (!h) return MPENV_ERR_INVALID;
+    NvtxRange nvtx("mpenv_step (Step graph)");
     MP_CUDA(h, cudaSetDevice(h->device));
     int rc = logsBeforeStep(h, (cudaStream_t)cuda_stream);
     if (rc != MPENV_OK) return rc;
@@ -630,6 +653,53 @@ int mpenv_stream_step(mpenv_handle *h, void *cuda_stream, void **buffers)
     return copyInterface(h, (cudaStream_t)cuda_stream, buffers, false);
 }
 
+int mpenv_check_guards(mpenv_handle *h, uint32_t *num_damaged)
+{
+    if (!h || !num_damaged) return MPENV_ERR_INVALID;
+    MP_CUDA(h, cudaSetDevice(h->device));
+    MP_CUDA(h, cudaStreamSynchronize(h->stream));
+    std::vector<unsigned char> host(2 * kGuardBytes);
+    uint32_t bad = 0;
+    for (const mpenv_handle::Guarded &g : h->guarded) {
+        const size_t padded = (g.bytes + 255) & ~(size_t)255;
+        MP_CUDA(h, cudaMemcpy(host.data(), g.raw, kGuardBytes, cudaMemcpyDeviceToHost));
+        // the tail band starts right after the buffer's last byte (the padding belongs to it)
+        const size_t tail = kGuardBytes + padded - g.bytes;
+        std::vector<unsigned char> t(tail);
+        MP_CUDA(h, cudaMemcpy(t.data(), g.raw + kGuardBytes + g.bytes, tail, cudaMemcpyDeviceToHost));
+        bool ok = true;
+        for (size_t i = 0; i < kGuardBytes; i++) ok = ok && host[i] == 0xA5;
+        for (size_t i = 0; i < tail; i++) ok = ok && t[i] == 0xA5;
+        if (!ok) bad++;
+    }
+    *num_damaged = bad;
+    return MPENV_OK;
+}
+
+// XLA GPU custom-call entry points (the ABI XLA binds: stream, buffers, opaque bytes).
+static mpenv_handle *xlaHandle(const char *opaque, size_t opaque_len)
+{
+    mpenv_handle *h = nullptr;
+    if (opaque && opaque_len == sizeof(h)) memcpy(&h, opaque, sizeof(h));
+    return h;
+}
+
+void mpenv_xla_init(void *cuda_stream, void **buffers, const char *opaque, size_t opaque_len)
+{
+    mpenv_handle *h = xlaHandle(opaque, opaque_len);
+    if (!h) { g_create_error = "mpenv_xla_init: opaque must hold the 8-byte mpenv_handle pointer"; return; }
+    if (mpenv_stream_init(h, cuda_stream, buffers) != MPENV_OK)
+        fprintf(stderr, "mpenv_xla_init: %s\n", h->error.c_str());
+}
+
+void mpenv_xla_step(void *cuda_stream, void **buffers, const char *opaque, size_t opaque_len)
+{
+    mpenv_handle *h = xlaHandle(opaque, opaque_len);
+    if (!h) { g_create_error = "mpenv_xla_step: opaque must hold the 8-byte mpenv_handle pointer"; return; }
+    if (mpenv_stream_step(h, cuda_stream, buffers) != MPENV_OK)
+        fprintf(stderr, "mpenv_xla_step: %s\n", h->error.c_str());
+}
+
 int mpenv_tensor(mpenv_handle *h, uint32_t export_id, mpenv_tensor_desc *out)
 {
     if (!h || !out) return MPENV_ERR_INVALID;
@@ -684,6 +754,7 @@ int mpenv_read_tensor_async(mpenv_handle *h, uint32_t export_id, void *host_dst,
 int mpenv_read_tensors_pipelined(mpenv_handle *h, const uint32_t *export_ids, void *const *host_dst, uint32_t n)
 {
     if (!h || !export_ids || !host_dst || n == 0 || n > 64) return MPENV_ERR_INVALID;
+    NvtxRange nvtx("mpenv_read_tensors_pipelined (snapshot + D2H)");
     MP_CUDA(h, cudaSetDevice(h->device));
     mpenv_tensor_desc d[64];
     size_t total = 0;

@@ -814,6 +814,13 @@ class GpuSim(_SimBase):
         self.lib.mpenv_launches_per_step(self.h, C.byref(a), C.byref(b))
         return a.value, b.value
 
+    def damaged_guards(self):
+        """Number of device buffers whose guard bands were written to (mpenv_check_guards)."""
+        n = C.c_uint32()
+        self.lib.mpenv_check_guards.argtypes = [C.c_void_p, C.POINTER(C.c_uint32)]
+        self._check(self.lib.mpenv_check_guards(self.h, C.byref(n)), "check_guards")
+        return n.value
+
     def episode_stats(self):
         """int64[16] episode statistics of this shard (k_stats), synchronous."""
         host = np.empty(16, np.int64)

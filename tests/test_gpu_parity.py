@@ -38,6 +38,7 @@ def rollout(W, steps, policy, flags=0, auto_reset=False, check_every=1, seed=10)
                 sim.step()
             if (s + 1) % check_every == 0 or s == steps - 1:
                 assert_same(gpu, orc, W, f"step {s}")
+        assert gpu.damaged_guards() == 0, "a kernel wrote outside its buffers (guard bands damaged)"
         return orc.export("match_result")
     finally:
         gpu.close(); orc.close()
@@ -145,6 +146,7 @@ def test_large_batch_properties():
                 dd = S.diff_world_state(gpu.world_state(off + w), orc.world_state(w))
                 assert not dd, f"world {off + w}: {dd[:8]}"
             orc.close()
+        assert gpu.damaged_guards() == 0, "a kernel wrote outside its buffers (guard bands damaged)"
     finally:
         gpu.close()
 
@@ -261,10 +263,24 @@ def test_python_manager_zero_copy_and_stream_step():
         assert lib.mpenv_stream_step(h, C.c_void_p(stream.cuda_stream), bufs) == 0
         stream.synchronize()
         orc.set_actions(d, a); orc.step()
-        for ours, theirs in (("self", "self_obs"), ("rewards", "reward"), ("fwd_lidar", "fwd_lidar"),
-                             ("opponents_last_known", "opponent_last_known_obs"), ("episode_results", "match_result")):
-            x = keep[ours].cpu().numpy().reshape(orc.export(theirs).shape)
-            assert np.array_equal(x.view(np.int32), orc.export(theirs).view(np.int32)), ours
+        def check_outputs(tag):
+            for ours, theirs in (("self", "self_obs"), ("rewards", "reward"), ("fwd_lidar", "fwd_lidar"),
+                                 ("opponents_last_known", "opponent_last_known_obs"), ("episode_results", "match_result")):
+                x = keep[ours].cpu().numpy().reshape(orc.export(theirs).shape)
+                assert np.array_equal(x.view(np.int32), orc.export(theirs).view(np.int32)), (tag, ours)
+        check_outputs("mpenv_stream_step")
+        # the XLA custom-call entry (bindings.cpp:149-158): void(stream, buffers, opaque, opaque_len),
+        # the handle pointer carried in `opaque`
+        d, a = S.random_actions(26, W)
+        keep["discrete"].copy_(torch.from_numpy(d).cuda()); keep["aim"].copy_(torch.from_numpy(a).cuda())
+        torch.cuda.synchronize()
+        lib.mpenv_xla_step.restype = None
+        lib.mpenv_xla_step.argtypes = [C.c_void_p, C.c_void_p, C.c_char_p, C.c_size_t]
+        opaque = C.string_at(C.byref(C.c_void_p(h.value)), 8)
+        lib.mpenv_xla_step(C.c_void_p(stream.cuda_stream), bufs, opaque, 8)
+        stream.synchronize()
+        orc.set_actions(d, a); orc.step()
+        check_outputs("mpenv_xla_step")
     finally:
         orc.close()
         del mgr
