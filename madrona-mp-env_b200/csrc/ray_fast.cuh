@@ -410,8 +410,19 @@ __device__ __forceinline__ int32_t walkChildren(const char *nd, const float tn[4
 
 // Pool interface (duck-typed):
 //   int  count()                                 rays in this warp's pool
-//   void load(int ray, RayRegs &r)               fill the lane's registers
-//   void finish(int ray, bool hit, float t)      closest mesh hit of a finished ray
+//   float load(int ray, RayRegs &r)              fill the lane's registers; returns the ray's initial t_max
+//   void finish(int ray, float t_max)            t_max of a finished ray (closest accepted hit, or the initial value)
+//
+// Initial t_max.  The reference starts every ray at FLT_MAX.  Starting at a finite bound U gives the
+// SAME final t whenever that t is below U: the visiting order is fixed (it does not depend on the
+// ray), so both runs see the same triangles in the same order, except those whose boxes the smaller
+// t_max culled or whose T <= t_max * det test it failed -- triangles at t >= U (1 - 4 delta), delta =
+// the relative rounding slop of those two tests (~1e-6).  By induction over that order, the two
+// runs' t_max are either equal or both >= U (1 - 4 delta); the first accepted triangle below that
+// level makes them equal for good.  So: final t < U (1 - 4 delta) => identical to the reference;
+// otherwise the reference's closest hit (if any) lies at >= U (1 - 4 delta).  A caller that only
+// needs "is there a hit at t <= tStop" (line of sight) starts at U = tStop (1 + 3e-4) and reads
+// t_max <= tStop: exact, and no box beyond the target is ever visited.
 // A ray that fails rayIsFast is traversed by the same loop with visitNodeRef instead of visitNode.
 //
 // Must be entered by all 32 lanes (warp-synchronous: ballots decide the batched
@@ -432,7 +443,7 @@ __device__ __forceinline__ void traversePool(const char *smem, const FastBVH &bv
     int32_t sp = 0;
     int32_t ray = -1;
     RayRegs r;
-    float t_max = FLT_MAX;           // FLT_MAX = no accepted hit yet (no hit lies that far in a bounded map)
+    float t_max = FLT_MAX;
     bool done = false;
     // the current node: meta word, children, t_near per slot and the slots still to consider (kept
     // in registers: the callers of this loop run at 80+ registers)
@@ -450,11 +461,10 @@ __device__ __forceinline__ void traversePool(const char *smem, const FastBVH &bv
         if ((idle_m | adv_m | pend_m) == 0) break;
         if (idle_m != 0 && (__popc(idle_m) >= kRefillBatch || adv_m == 0)) {
             if (idle) {
-                if (ray >= 0) pool.finish(ray, t_max != FLT_MAX, t_max);
+                if (ray >= 0) pool.finish(ray, t_max);
                 ray = next_ray + __popc(idle_m & lane_lt);
                 if (ray < pool_count) {
-                    pool.load(ray, r);
-                    t_max = FLT_MAX;
+                    t_max = pool.load(ray, r);
                     stack[0] = 0;
                     sp = 1;
                 } else {

@@ -66,15 +66,16 @@ struct LosPoolAccess {
     int32_t n;
     __device__ __forceinline__ int count() const { return n; }
     uint32_t dirsOff;                // shared-memory offset of P->dirs
-    __device__ __forceinline__ void load(int ray, RayRegs &r)
+    __device__ __forceinline__ float load(int ray, RayRegs &r)
     {
         const float4 o = P->origin[P->meta[ray] & 15];
         const RayDirRec &d = P->dirs[ray];
         setRay(r, o.x, o.y, o.z, d.invX, d.invY, d.invZ,
                dirsOff + (uint32_t)ray * (uint32_t)sizeof(RayDirRec) + (uint32_t)offsetof(RayDirRec, tri));
         r.tStop = P->tstop[ray];
+        return r.tStop * 1.0003f;        // nothing beyond the target matters (see traversePool)
     }
-    __device__ __forceinline__ void finish(int ray, bool hit, float t) { P->tmesh[ray] = hit ? t : -1.f; }
+    __device__ __forceinline__ void finish(int ray, float t_max) { P->tmesh[ray] = t_max; }
 };
 
 template <int kBatch, int kRefill>
@@ -196,8 +197,7 @@ __global__ void __launch_bounds__(kLosWarpsPerCTA * 32, MPENV_LOS_MINB) k_los_po
             // ---- phase 3: visible unless a mesh hit at t <= t_target was accepted
             for (int32_t ray = lane; ray < n; ray += 32) {
                 const int32_t pair = P.meta[ray] >> 8;
-                const float tm = P.tmesh[ray];
-                if (!(tm >= 0.f && tm <= P.tstop[ray])) atomicOr(&P.seen[pair >> 5], 1u << (pair & 31));
+                if (!(P.tmesh[ray] <= P.tstop[ray])) atomicOr(&P.seen[pair >> 5], 1u << (pair & 31));
             }
             __syncwarp();
         }

@@ -97,3 +97,41 @@ void exp_trace(void *h, int64_t n, const float *o, const float *d, const float *
 }
 int exp_num_nodes(void *h) { return (int)((HostSim *)h)->ctx.bvh.numNodes; }
 }
+
+// EXPERIMENT: line-of-sight rays that an early-out after the first visible sample would skip.
+extern "C" void exp_los_stats(void *h, int64_t *out)
+{
+    HostSim &s = *(HostSim *)h;
+    const Ctx &c = s.ctx; const SimPtrs &p = c.p; const float *fr = c.mc->frustum;
+    int64_t rays = 0, skip_after_first = 0, skip_if_s0 = 0, pairs_traced = 0, pairs_visible = 0, vis_rays = 0;
+    for (int w = 0; w < (int)s.numWorlds; w++) {
+        const Vec3 *wp = p.pos + (size_t)w * kAgents; const int base = w * kAgents;
+        for (int a = 0; a < kAgents; a++) for (int j = 0; j < kTeamSize; j++) {
+            const int idx = base + a; const int opp = (teamOf(a) ^ 1) * kTeamSize + j;
+            if (p.alive[idx] == 0.f || p.alive[base + opp] == 0.f) continue;
+            Vec3 o = wp[a]; o.z += viewHeight(p.stand[idx].cur);
+            const Aim aim = p.aim[idx]; const Quat inv = quatInv(aim.rot);
+            const float vh = viewHeight(p.stand[base + opp].cur);
+            Vec3 dr = rotateVec(aim.rot, kRight()) * 0.9f * kAgentRadius;
+            bool seen = false; int n = 0; bool vis0 = false;
+            for (int sidx = 0; sidx < 4; sidx++) {
+                Vec3 pt = losSamplePoint(wp[opp], vh, dr, sidx);
+                Vec3 tt = pt - o; Vec3 vp = rotateVec(inv, tt);
+                if (vp.y <= 0.f) continue;
+                if (!(vp.y * fr[1] - fabsf(vp.x) * fr[0] > -kAgentRadius)) continue;
+                if (!(vp.y * fr[3] - fabsf(vp.z) * fr[2] > -kAgentRadius)) continue;
+                if (length(tt) < kAgentRadius) continue;
+                rays++; n++;
+                if (seen) skip_after_first++;
+                if (vis0 && sidx > 0) skip_if_s0++;
+                bool v = losSampleVisible(c, wp, o, inv, pt, opp);
+                if (v) vis_rays++;
+                if (v && sidx == 0) vis0 = true;
+                if (v) seen = true;
+            }
+            if (n) pairs_traced++;
+            if (seen) pairs_visible++;
+        }
+    }
+    out[0] = rays; out[1] = skip_after_first; out[2] = skip_if_s0; out[3] = pairs_traced; out[4] = pairs_visible; out[5] = vis_rays;
+}
