@@ -28,7 +28,8 @@ extern "C" {
 #define MPENV_ERR_IO (-2)        /* asset file missing or corrupt */
 #define MPENV_ERR_CUDA (-3)      /* CUDA runtime error (no device, OOM, launch failure) */
 
-/* Task (reference src/types.hpp:45-51); only MPENV_TASK_ZONE is implemented. */
+/* Task (reference src/types.hpp:45-51); MPENV_TASK_ZONE and MPENV_TASK_ZONE_CAPTURE_DEFEND (needs a map with
+ * >= 4 zones: the objective is pinned to zone 3, sim.cpp:822-825) are implemented. */
 #define MPENV_TASK_EXPLORE 0
 #define MPENV_TASK_TDM 1
 #define MPENV_TASK_ZONE 2
@@ -57,7 +58,7 @@ typedef struct mpenv_config {
     uint32_t rand_seed;          /* Config::randSeed */
     int32_t auto_reset;          /* Config::autoReset */
     uint32_t sim_flags;          /* Config::simFlags */
-    uint32_t task_type;          /* Config::taskType; must be MPENV_TASK_ZONE */
+    uint32_t task_type;          /* Config::taskType; MPENV_TASK_ZONE or MPENV_TASK_ZONE_CAPTURE_DEFEND */
     uint32_t team_size;          /* Config::teamSize; must be 6 */
     uint32_t num_pbt_policies;   /* Config::numPBTPolicies (carried, unused by the step) */
     uint32_t policy_history_size;/* Config::policyHistorySize (carried, unused) */

@@ -324,6 +324,7 @@ struct SimConfig {
     int32_t replayLog;                  // TaskConfig::replayLog != nullptr
     int32_t numCurriculumSnapshots;     // TrajectoryCurriculum::numSnapshots (mgr.cpp:1419-1441)
     int32_t rewardFlank;                // TaskConfig::rewardMode == RewardMode::Flank (mgr.cpp:1745-1750)
+    int32_t taskCaptureDefend;          // TaskConfig::task == Task::ZoneCaptureDefend (else Task::Zone)
 };
 
 // TrainControl (types.hpp:158), live tensor (mgr.cpp:287-293)

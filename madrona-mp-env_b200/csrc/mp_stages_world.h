@@ -603,6 +603,20 @@ MP_HD void zoneMatchInfoSystem(const Ctx &c, int w)
     if (mr.teamObjectivePoints[0] >= kZoneWinPoints || mr.teamObjectivePoints[1] >= kZoneWinPoints) {
         match_finished = true;
     }
+    // Task::ZoneCaptureDefend (sim.cpp:4534-4573): the attackers (team A) win on their first
+    // objective point, the defenders at 8 or once every attacker has died during the episode.
+    constexpr int32_t capdefend_attacker_win = 1, capdefend_defender_win = 8;
+    const int32_t attacker_team = mi.teamA == 1 ? 1 : 0, defender_team = attacker_team ^ 1;
+    bool team_has_all_died[2] = { true, true };
+    const bool capdefend = kCold && c.cfg.taskCaptureDefend;
+    if (capdefend) {
+        if (mr.teamObjectivePoints[attacker_team] == capdefend_attacker_win) match_finished = true;
+        if (mr.teamObjectivePoints[defender_team] == capdefend_defender_win) match_finished = true;
+        for (int i = 0; i < kAgents; i++) {
+            if (!p.combat[base + i].hasDiedDuringEpisode) team_has_all_died[teamOf(i)] = false;
+        }
+        if (team_has_all_died[attacker_team]) match_finished = true;
+    }
     {
         ZoneStats &st = ws.zoneStats[zs.curZone];
         st.activeSteps += 1;
@@ -613,7 +627,12 @@ MP_HD void zoneMatchInfoSystem(const Ctx &c, int w)
         if (kCold && c.cfg.eventLog) logWorldEvents(c, w, new_captured);      // sim.cpp:4592-4634
     }
     if (match_finished) {
-        if (mr.teamObjectivePoints[0] > mr.teamObjectivePoints[1]) mr.winResult = 0;
+        if (capdefend) {                                   // sim.cpp:4637-4646
+            if (mr.teamObjectivePoints[attacker_team] == capdefend_attacker_win) mr.winResult = attacker_team;
+            else if (mr.teamObjectivePoints[defender_team] == capdefend_defender_win ||
+                     team_has_all_died[attacker_team]) mr.winResult = defender_team;
+            else mr.winResult = 2;
+        } else if (mr.teamObjectivePoints[0] > mr.teamObjectivePoints[1]) mr.winResult = 0;
         else if (mr.teamObjectivePoints[1] > mr.teamObjectivePoints[0]) mr.winResult = 1;
         else mr.winResult = 2;
         for (int z = 0; z < kMaxZones; z++) {
@@ -824,6 +843,54 @@ MP_HD void zoneRewardSystem(const Ctx &c, int w, int a)
     p.reward[idx] = reward;
 }
 
+// zoneCaptureDefendRewardSystem (sim.cpp:4089-4209): Task::ZoneCaptureDefend's per-agent reward
+// (goal-region progress of the agent's team, kills / hits, exploration, zone control for the
+// controlling team only, +-20 / -5 at the end of the match).
+MP_HD void zoneCaptureDefendRewardSystem(const Ctx &c, int w, int a)
+{
+    const SimPtrs &p = c.p;
+    const MapConsts &mc = *c.mc;
+    const int idx = w * kAgents + a;
+    CombatState &cs = p.combat[idx];
+    const WorldState &ws = p.world[w];
+    const RewardHyperParams hp = p.rewardCoefs[idx];
+    float reward = 0.f;
+    reward += 0.02f * ws.goalTeamStepRewards[teamOf(a)];
+    if (cs.reloadedFullMag) reward -= 0.01f;
+    if (cs.successfulKill) reward += 1.f;
+    if (cs.landedShotOn != -1) reward += hp.shotScale * 1.f;
+    if (cs.wasKilled) reward -= 1.f;
+    if (cs.wasShotCount > 0) reward -= hp.shotScale * 1.f;
+    uint32_t num_new_cells = p.exploreNew[idx];
+    p.exploreNew[idx] = 0;
+    if (num_new_cells > 0) reward += float(num_new_cells) * hp.exploreScale;
+    const ZoneState &zs = ws.zone;
+    if (!cs.inZone) {
+        AABB zb = mc.zoneBoxes[zs.curZone];
+        Vec3 center = (zb.pMax + zb.pMin) / 2.f;
+        float dist = distance(center, p.pos[idx]);
+        if (dist < cs.minDistToZone) cs.minDistToZone = dist;
+    }
+    if (zs.curControllingTeam != -1 && zs.curControllingTeam == teamOf(a)) {
+        reward += hp.zoneTeamCtrlScale;
+        if (zs.earnedPoint) reward += hp.zoneEarnedPointScale;
+    }
+    if (ws.match.isFinished) {
+        const int32_t win = p.matchResult[w].winResult;
+        if (win == 2) reward -= 5.f;
+        else if (win == teamOf(a)) reward += 20.f;
+        else reward -= 20.f;
+    }
+    if (p.alive[idx] == 0.f) {
+        cs.successfulKill = 0;
+        cs.landedShotOn = -1;
+        cs.wasKilled = 0;
+        cs.wasShotCount = 0;
+        cs.firedShotT = -FLT_MAX;
+    }
+    p.reward[idx] = reward;
+}
+
 // pvpTeamRewardSystem + pvpFinalRewardSystem (sim.cpp:4292-4339)
 MP_HD void teamAndFinalReward(const Ctx &c, int w)
 {
@@ -925,6 +992,7 @@ MP_HD void initWorld(const Ctx &c, int w, bool triggered_reset)
     zs.earnedPoint = 0;
     zs.zoneStepsRemaining = kNumStepsPerZone;
     zs.stepsUntilPoint = kZonePointInterval;
+    if (c.cfg.taskCaptureDefend) zs.curZone = 3;       // sim.cpp:822-825 (after the draw: the RNG count is unchanged)
 
     // ---- resetPersistentEntities
     for (int i = 0; i < kAgents; i++) {
@@ -1111,7 +1179,8 @@ MP_HD void stageWorld(const Ctx &c, int w)
     evaluateGoalRegionsSystem(c, w);
     for (int i = 0; i < kAgents; i++) exploreVisitedSystem(c, w, base + i);
     for (int i = 0; i < kAgents; i++) {
-        if (c.cfg.rewardFlank) flankRewardSystem(c, w, i);
+        if (c.cfg.taskCaptureDefend) zoneCaptureDefendRewardSystem(c, w, i);
+        else if (c.cfg.rewardFlank) flankRewardSystem(c, w, i);
         else zoneRewardSystem(c, w, i);
     }
     teamAndFinalReward(c, w);

@@ -330,7 +330,8 @@ int mpenv_create(const mpenv_config *cfg, mpenv_handle **out)
 {
     NvtxRange nvtx("mpenv_create");
     if (!cfg || !out || !cfg->scene_dir) return fail(nullptr, MPENV_ERR_INVALID, "null argument");
-    if (cfg->task_type != MPENV_TASK_ZONE) return fail(nullptr, MPENV_ERR_INVALID, "only Task::Zone is implemented");
+    if (cfg->task_type != MPENV_TASK_ZONE && cfg->task_type != MPENV_TASK_ZONE_CAPTURE_DEFEND)
+        return fail(nullptr, MPENV_ERR_INVALID, "only Task::Zone and Task::ZoneCaptureDefend are implemented");
     if (cfg->team_size != (uint32_t)kTeamSize) return fail(nullptr, MPENV_ERR_INVALID, "team_size must be 6");
     if (cfg->num_worlds == 0 || cfg->num_worlds > (1u << 22)) return fail(nullptr, MPENV_ERR_INVALID, "num_worlds out of range");
     const uint32_t unsupported = MPENV_FLAG_SPAWN_IN_MIDDLE | MPENV_FLAG_NAVMESH_SPAWN |
@@ -355,7 +356,7 @@ int mpenv_create(const mpenv_config *cfg, mpenv_handle **out)
     h->recordLog = cfg->record_log_path != nullptr;
     h->replayLog = cfg->replay_log_path != nullptr;
     h->cold = h->eventLog || h->recordLog || h->replayLog || cfg->curriculum_data_path != nullptr ||
-              cfg->train_flank != 0;
+              cfg->train_flank != 0 || cfg->task_type == MPENV_TASK_ZONE_CAPTURE_DEFEND;
     if (h->eventLog) h->eventDir = cfg->event_log_dir;
     if (h->recordLog) h->recordPath = cfg->record_log_path;
     if (h->replayLog) h->replayPath = cfg->replay_log_path;
@@ -370,6 +371,13 @@ int mpenv_create(const mpenv_config *cfg, mpenv_handle **out)
     if (!loadMapAssets(h->sceneDir, &h->assets, &err) || !fillMapConsts(h->assets, &h->hostConsts, &err)) {
         h->error = err;
         return bail(MPENV_ERR_IO);
+    }
+    if (cfg->task_type == MPENV_TASK_ZONE_CAPTURE_DEFEND && h->hostConsts.numZones < 4) {
+        // initWorld pins the objective to zone 3 (sim.cpp:822-825)
+        h->error = "Task::ZoneCaptureDefend needs a map with at least 4 zones (zones.bin has " +
+                   std::to_string(h->hostConsts.numZones) + ")";
+        g_create_error = h->error;
+        return bail(MPENV_ERR_INVALID);
     }
 
 #define MP_CREATE(call) do { if (!cudaOk(h, (call), #call)) return bail(MPENV_ERR_CUDA); } while (0)
@@ -423,6 +431,7 @@ int mpenv_create(const mpenv_config *cfg, mpenv_handle **out)
     ka.ctx.cfg.recordLog = h->recordLog ? 1 : 0;
     ka.ctx.cfg.replayLog = h->replayLog ? 1 : 0;
     ka.ctx.cfg.rewardFlank = cfg->train_flank ? 1 : 0;
+    ka.ctx.cfg.taskCaptureDefend = cfg->task_type == MPENV_TASK_ZONE_CAPTURE_DEFEND ? 1 : 0;
 
     // navmesh + A* table for the scripted bot (LevelData, sim.cpp:5895-5898)
     if (h->assets.hasNav) {

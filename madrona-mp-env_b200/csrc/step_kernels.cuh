@@ -183,7 +183,8 @@ __global__ void __launch_bounds__(128) k_world(KernelArgs ka)
         evaluateGoalRegionsCoop(c, w, lane, half, valid);
         if (agent) {
             exploreVisitedSystem(c, w, base + lane);
-            if (kCold && c.cfg.rewardFlank) flankRewardSystem(c, w, lane);
+            if (kCold && c.cfg.taskCaptureDefend) zoneCaptureDefendRewardSystem(c, w, lane);
+            else if (kCold && c.cfg.rewardFlank) flankRewardSystem(c, w, lane);
             else zoneRewardSystem(c, w, lane);
         }
         __syncwarp();

@@ -66,6 +66,7 @@ struct HostSimConfig {
     uint32_t numCurriculumSnapshots;
     const void *curriculumSnapshots;
     uint32_t trainFlank;
+    uint32_t taskType;          // 2 = Zone, 4 = ZoneCaptureDefend
 };
 
 void *hostsim_create(const HostSimConfig *cfg, const char *scene_dir)
@@ -90,6 +91,7 @@ void *hostsim_create(const HostSimConfig *cfg, const char *scene_dir)
     c.cfg.recordLog = cfg->enableRecordLog ? 1 : 0;
     c.cfg.replayLog = cfg->enableReplayLog ? 1 : 0;
     c.cfg.rewardFlank = cfg->trainFlank ? 1 : 0;
+    c.cfg.taskCaptureDefend = cfg->taskType == 4 ? 1 : 0;
     c.mc = &s->consts;
     c.bvh.nodes = s->assets.nodes.data();
     c.bvh.verts = s->assets.verts.data();

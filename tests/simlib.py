@@ -179,6 +179,30 @@ def build_oracle():
 
 
 # ---------------------------------------------------------------------- map
+def make_scene(dst_dir, zones):
+    """A copy of data/simple_map with its own zones.bin (map_importer.cpp:545-561: u32 n, AABB[n],
+    f32 rotation[n]).  zones: [(xmin, ymin, zmin, xmax, ymax, zmax, rotation), ...]."""
+    import shutil
+    os.makedirs(dst_dir, exist_ok=True)
+    for f in os.listdir(SCENE):
+        if f != "zones.bin":
+            shutil.copy(os.path.join(SCENE, f), os.path.join(dst_dir, f))
+    z = np.asarray(zones, np.float32).reshape(-1, 7)
+    with open(os.path.join(dst_dir, "zones.bin"), "wb") as fh:
+        fh.write(np.uint32(len(z)).tobytes())
+        fh.write(np.ascontiguousarray(z[:, :6]).tobytes())
+        fh.write(np.ascontiguousarray(z[:, 6]).tobytes())
+    return dst_dir
+
+
+# simple_map's three zones plus a fourth around the eastern platform, rotated 0.3 rad: the map
+# Task::ZoneCaptureDefend needs (its objective is zone 3, sim.cpp:822-825)
+FOUR_ZONES = [(-759.59906, -488.75443, -10.08213, 759.59906, 488.75443, 383.38632, 0.0),
+              (-1953.6677, -1051.0848, -10.08213, -1114.1248, 1051.0848, 383.38632, 0.0),
+              (1107.1403, -1051.0848, -10.08213, 1946.6832, 1051.0848, 383.38632, 0.0),
+              (-600.0, 500.0, -10.0, 700.0, 1500.0, 380.0, 0.3)]
+
+
 class MapInfo(C.Structure):
     _fields_ = [("num_nodes", C.c_uint32), ("num_tris", C.c_uint32), ("num_leaves", C.c_uint32),
                 ("root_aabb", C.c_float * 6), ("world_bounds", C.c_float * 6),
@@ -339,7 +363,7 @@ class Oracle(_SimBase):
     def __init__(self, num_worlds, rand_seed=10, auto_reset=False, sim_flags=0, det=True,
                  world_id_offset=0, num_threads=1, scene=SCENE, bvh=None, event_log=False,
                  record_log=False, replay_log=False, curriculum=None, navmesh=True, train_flank=False,
-                 fast=False):
+                 fast=False, task=2):
         """fast=True (with det=False): the -O3 build of the libm oracle, for timing only."""
         build_oracle()
         assert not (fast and det), "the timed -O3 build exists for the libm arithmetic only"
@@ -367,7 +391,7 @@ class Oracle(_SimBase):
         nodes, verts, info = bvh
         v20 = np.zeros((verts.shape[0], 5), dtype=np.float32)     # BVHVertex {pos, uv}
         v20[:, :3] = verts
-        cfg = RefConfig(num_worlds, rand_seed, int(auto_reset), sim_flags, 2, 6, 0, 1,
+        cfg = RefConfig(num_worlds, rand_seed, int(auto_reset), sim_flags, int(task), 6, 0, 1,
                         world_id_offset, num_threads, int(event_log), int(record_log), int(replay_log),
                         0 if curriculum is None else len(curriculum),
                         None if curriculum is None else np.ascontiguousarray(curriculum).ctypes.data)
@@ -489,7 +513,7 @@ class HostSimConfig(C.Structure):
                 ("simFlags", C.c_uint32), ("worldIDOffset", C.c_uint32), ("enableFullTeam", C.c_uint32),
                 ("enableEventLog", C.c_uint32), ("enableRecordLog", C.c_uint32),
                 ("enableReplayLog", C.c_uint32), ("numCurriculumSnapshots", C.c_uint32),
-                ("curriculumSnapshots", C.c_void_p), ("trainFlank", C.c_uint32)]
+                ("curriculumSnapshots", C.c_void_p), ("trainFlank", C.c_uint32), ("taskType", C.c_uint32)]
 
 
 class HostSim(_SimBase):
@@ -497,7 +521,7 @@ class HostSim(_SimBase):
 
     def __init__(self, num_worlds, rand_seed=10, auto_reset=False, sim_flags=0, world_id_offset=0,
                  full_team=True, scene=SCENE, event_log=False, record_log=False, replay_log=False,
-                 curriculum=None, train_flank=False):
+                 curriculum=None, train_flank=False, task=2):
         self.lib = C.CDLL(build_hostsim())
         L = self.lib
         L.hostsim_create.restype = C.c_void_p
@@ -514,7 +538,7 @@ class HostSim(_SimBase):
                             int(full_team), int(event_log), int(record_log), int(replay_log),
                             0 if curriculum is None else len(curriculum),
                             None if curriculum is None else np.ascontiguousarray(curriculum).ctypes.data,
-                            int(train_flank))
+                            int(train_flank), int(task))
         L.hostsim_read_event_log.restype = C.c_int64
         L.hostsim_read_event_log.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint64]
         L.hostsim_record_log.restype = C.c_void_p
@@ -740,7 +764,7 @@ class GpuSim(_SimBase):
 
     def __init__(self, num_worlds, rand_seed=10, auto_reset=False, sim_flags=0, world_id_offset=0,
                  full_team=True, scene=SCENE, gpu_id=0, event_log=False, record_log=False, replay_log=False,
-                 curriculum_path=None, train_flank=False, instrumented=False):
+                 curriculum_path=None, train_flank=False, instrumented=False, task=2):
         """instrumented: load libmpenv_b200_count.so (mpenv_ray_counts works there).
         event_log / record_log / replay_log: False = off, True = in memory only,
         a path = the reference's files (event_log: directory)."""
@@ -749,7 +773,7 @@ class GpuSim(_SimBase):
         path = lambda v: None if v is False or v is None else (b"" if v is True else str(v).encode())
         self._log_paths = [path(event_log), path(record_log), path(replay_log),
                            None if curriculum_path is None else str(curriculum_path).encode()]
-        cfg = MpenvConfig(gpu_id, num_worlds, rand_seed, int(auto_reset), sim_flags, 2, 6, 0, 1,
+        cfg = MpenvConfig(gpu_id, num_worlds, rand_seed, int(auto_reset), sim_flags, int(task), 6, 0, 1,
                           self._scene, world_id_offset, int(full_team), *self._log_paths, int(train_flank))
         self.h = C.c_void_p()
         rc = self.lib.mpenv_create(C.byref(cfg), C.byref(self.h))

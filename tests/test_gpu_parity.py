@@ -362,3 +362,20 @@ def test_large_map_fallback_kernels(monkeypatch):
                 assert_same(gpu, orc, W, f"legacy step {s}")
     finally:
         gpu.close(); orc.close()
+
+
+@pytest.mark.parametrize("variant,flags", [("north", 0), ("south", 128), ("sky", 8)])
+def test_zone_capture_defend_gpu(tmp_path, variant, flags):
+    """Task::ZoneCaptureDefend (SURVEY 8f-4) on the synthetic 4-zone map: defender win at 8 points,
+    attacker win on the first point, "all attackers have died" -- see test_hostsim_parity.py."""
+    from test_hostsim_parity import zone_capture_defend_rollout
+    outcomes = zone_capture_defend_rollout(
+        lambda W, f, scene: S.GpuSim(W, sim_flags=f, auto_reset=True, scene=scene, task=4),
+        str(tmp_path / "four_zones"), variant, flags, assert_same)
+    expect = {"north": (False, 8), "south": (True, 1), "sky": (False, 0)}[variant]
+    assert expect in outcomes, f"{variant}: outcomes {outcomes}"
+
+
+def test_zone_capture_defend_needs_four_zones():
+    with pytest.raises(RuntimeError, match="at least 4 zones"):
+        S.GpuSim(2, task=4)

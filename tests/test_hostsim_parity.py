@@ -145,3 +145,55 @@ def test_libm_oracle_within_tolerance(built):
     stats = bridge.run_bridge(lambda: S.Oracle(32, det=True, num_threads=0), W=32, steps=1000)
     stats.check_budgets()
     assert stats.flips["fwd_lidar"] > 0, "no discontinuity flip in 1000 steps: the comparison is not seeing the lidar"
+
+
+def zone_capture_defend_rollout(make_ours, scene_dir, variant, flags, assert_same_fn):
+    """Task::ZoneCaptureDefend (SURVEY 8f-4; sim.cpp:822-825, 4089-4209, 4534-4573, 4637-4646) on a
+    synthetic 4-zone copy of simple_map; the objective is pinned to zone 3.  variant:
+      north   zone 3 next to the defenders' side: they win at 8 objective points;
+      south   zone 3 next to the attackers' side: they win on their first point;
+      sky     zone 3 out of reach (no points): at step 40 every attacker of worlds 0 and 2 gets
+              hp = 0 through the exported hp tensor -> "all attackers have died" ends the match."""
+    zones = list(S.FOUR_ZONES)
+    if variant == "south":
+        zones[3] = (-600.0, -1500.0, -10.0, 700.0, -500.0, 380.0, 0.3)
+    elif variant == "sky":
+        zones[3] = (-100.0, -100.0, 300.0, 100.0, 100.0, 380.0, 0.0)
+    scene = S.make_scene(scene_dir, zones)
+    W = 4
+    ours = make_ours(W, flags, scene)
+    orc = S.Oracle(W, sim_flags=flags, auto_reset=True, det=True, scene=scene, task=4)
+    outcomes = set()
+    try:
+        ours.init(); orc.init()
+        assert_same_fn(ours, orc, W, "init")
+        for s in range(260 if variant != "sky" else 60):
+            d, a = S.seek_policy(orc, s, W)
+            if variant == "sky" and s == 40:
+                hp = orc.export("hp")
+                team_a = [orc.world_state(w)["team_a"] for w in (0, 2)]
+                for w, ta in zip((0, 2), team_a):
+                    hp[w * 12 + ta * 6: w * 12 + ta * 6 + 6] = 0.0
+                for sim in (ours, orc):
+                    sim.set_export("hp", hp)
+            for sim in (ours, orc):
+                sim.set_actions(d, a); sim.step()
+            if s % 20 == 19 or (variant == "sky" and s in (40, 41)):
+                assert_same_fn(ours, orc, W, f"step {s}")
+            done = orc.export("done").reshape(W, 12)[:, 0]
+            mr = orc.export("match_result")
+            for w in np.flatnonzero(done):
+                outcomes.add((int(mr[w, 0]) == orc.world_state(int(w))["team_a"], int(mr[w, 3] + mr[w, 4])))
+        assert orc.world_state(1)["zone_cur"] == 3
+    finally:
+        ours.close(); orc.close()
+    return outcomes        # {(attacker won?, objective points scored)}
+
+
+@pytest.mark.parametrize("variant,flags", [("north", 0), ("south", 128), ("sky", 0), ("sky", 8)])
+def test_zone_capture_defend(built, tmp_path, variant, flags):
+    outcomes = zone_capture_defend_rollout(
+        lambda W, f, scene: S.HostSim(W, sim_flags=f, auto_reset=True, scene=scene, task=4),
+        str(tmp_path / "four_zones"), variant, flags, assert_same)
+    expect = {"north": (False, 8), "south": (True, 1), "sky": (False, 0)}[variant]
+    assert expect in outcomes, f"{variant}: outcomes {outcomes}"
