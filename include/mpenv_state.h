@@ -71,6 +71,8 @@ typedef struct mpenv_agent_state {
     int32_t team_offset;
     int32_t policy;
     float reward_coefs[9];
+    int32_t in_sub_zone;             /* CombatState::inSubZone / minDistToSubZone (SimFlags::SubZones) */
+    float min_dist_to_sub_zone;
 } mpenv_agent_state;
 
 typedef struct mpenv_breadcrumb_state {
@@ -115,6 +117,8 @@ typedef struct mpenv_world_state {
     float goal_min_dist[2];
     float goal_team_step_rewards[2];
     float team_rewards[2];
+    /* SubZone x 8: curControllingTeam, isContested, isCaptured (types.hpp:791-796) */
+    int32_t sub_zones[8][3];
     /* SpawnUsageCounter */
     uint32_t spawn_a_last_used[MPENV_MAX_SPAWNS];
     uint32_t spawn_b_last_used[MPENV_MAX_SPAWNS];

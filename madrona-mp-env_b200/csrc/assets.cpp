@@ -391,6 +391,20 @@ bool fillMapConsts(const MapAssets &assets, MapConsts *mc, std::string *err)
     }
     // mgr.cpp:913-944
     const float top = -56.f + kStandHeight * 1.5f;
+    {   // createPersistentEntities, level_gen.cpp:279-322 (SimFlags::SubZones); a map with fewer than
+        // three zones cannot run that flag (mpenv_create refuses it)
+        const size_t nz = assets.zoneBoxes.size();
+        for (int k = 0; k < 2; k++) {
+            const size_t z = (size_t)k + 1 < nz ? (size_t)k + 1 : 0;
+            mc->subZones[k] = { assets.zoneBoxes[z].pMin, assets.zoneBoxes[z].pMax, assets.zoneRots[z] };
+        }
+        mc->subZones[2] = { { -950, -500, 0 }, { -50, 500, 1000 }, 0.f };
+        mc->subZones[3] = { { 50, -500, 0 }, { 950, 500, 1000 }, 0.f };
+        mc->subZones[4] = { { -1000, -1650, 0 }, { -50, -600, 1000 }, 0.f };
+        mc->subZones[5] = { { 50, -1650, 0 }, { 1000, -600, 1000 }, 0.f };
+        mc->subZones[6] = { { -1000, 600, 0 }, { -50, 1650, 1000 }, 0.f };
+        mc->subZones[7] = { { 1000, 600, 0 }, { 50, 1650, 1000 }, 0.f };      // pMin.x > pMax.x in the reference too
+    }
     mc->numGoalRegions = 2;
     mc->goalRegions[0].sub[0] = { { 625, 510, -64 }, { 900, 540, top }, 0.f };
     mc->goalRegions[0].numSub = 1;

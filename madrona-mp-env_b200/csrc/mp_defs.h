@@ -105,6 +105,11 @@ struct CombatState {                                            // types.hpp:510
     int32_t reloadedFullMag;
     int32_t weaponType;
 };
+// SimFlags::SubZones state (types.hpp:791-796; CombatState::inSubZone / minDistToSubZone, types.hpp:510),
+// kept apart from CombatState / WorldState so that the default step does not carry it.
+constexpr int kNumSubZones = 8;                                 // sim.hpp:190
+struct SubZoneAgentState { int32_t inSubZone; float minDistToSubZone; };
+struct SubZoneState { int32_t curControllingTeam, isContested, isCaptured; };
 struct CrumbAgentState {                                        // types.hpp:772
     float totalPenalty;
     uint32_t lastCrumbUID;       // 0 = Entity::none()
@@ -305,6 +310,7 @@ struct MapConsts {
     float zoneRots[kMaxZones];
     GoalRegion goalRegions[2];
     int32_t numGoalRegions;
+    ZOBB subZones[kNumSubZones];        // level_gen.cpp:279-322 (two from zones 1 / 2, six hard-coded)
     WeaponStats weapons[kMaxWeaponTypes];
     int32_t numWeaponTypes;
     // lidar direction tables: -cos(theta), sin(theta) per column
@@ -336,6 +342,7 @@ struct SimPtrs {
     Vec3 *pos; Quat *rot; Vec3 *vel; MoveState *move; Aim *aim;
     float *hp; float *alive; Magazine *mag; float *dmg;   // dmg: [N][6]
     StandState *stand; CombatState *combat; CrumbAgentState *crumbAgent;
+    SubZoneAgentState *subZoneAgent;     // SimFlags::SubZones only
     Vec3 *startPos; uint32_t *exploreGrid; uint32_t *exploreNew;
     uint8_t *canSee;                     // [N][8] (6 used)
     int32_t *policy; RewardHyperParams *rewardCoefs;
@@ -350,6 +357,7 @@ struct SimPtrs {
     // per world
     WorldState *world; SpawnUsage *spawnUsage; Crumb *crumbs;
     MatchResult *matchResult; int32_t *resetFlag; int32_t *worldCurriculum;
+    SubZoneState *subZones;              // [W][8], SimFlags::SubZones only
     // per team (2 per world), full-team interface
     FullTeamGlobalObs *ftGlobal; FullTeamPlayerObs *ftPlayers; FullTeamEnemyObs *ftEnemies;
     FullTeamCommonObs *ftLastKnown; LidarSample *ftFwdLidar; LidarSample *ftRearLidar;

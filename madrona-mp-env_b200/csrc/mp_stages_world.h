@@ -239,6 +239,13 @@ MP_HD void standardSpawnPoint(const Ctx &c, int w, int a, bool is_respawn, Vec3 
     *out_yaw = sp.yawMin + yaw_rnd * (sp.yawMax - sp.yawMin);
 }
 
+// The sub-zone an agent is assigned to: its policy id clamped to the sub-zone range (sim.cpp:1996-1997).
+MP_HD int subZoneOf(const SimPtrs &p, int idx)
+{
+    const int32_t k = p.policy[idx];
+    return k < 0 ? 0 : (k > kNumSubZones - 1 ? kNumSubZones - 1 : k);
+}
+
 // Zone-frame AABB of the current zone (shared by zoneSystem / spawnAgents).
 MP_HD void zoneFrame(const MapConsts &mc, int32_t zone, Quat *to_zone, AABB *box)
 {
@@ -316,6 +323,18 @@ MP_HD void spawnAgents(const Ctx &c, int w, bool is_respawn)
             cs.inZone = aabbContains(zbox, pos_in_zone) ? 1 : 0;
             cs.minDistToZone = distance(spawn_pt, zone_center);
         }
+        if (c.cfg.simFlags & kFlagSubZones) {
+            // utils.cpp:906-926: the agent's sub-zone is its policy id clamped to 0..7; spawn_pt has
+            // already been raised by half the stand height above and is raised once more here
+            const ZOBB &sz = mc.subZones[subZoneOf(p, idx)];
+            Vec3 zone_center = (sz.pMax + sz.pMin) / 2.f;
+            Quat to_zone = quatInv(angleAxis(sz.rotation, kUp()));
+            AABB zbox; zbox.pMin = rotateVec(to_zone, sz.pMin); zbox.pMax = rotateVec(to_zone, sz.pMax);
+            Vec3 pos_in_zone = rotateVec(to_zone, spawn_pt);
+            spawn_pt.z += kStandHeight / 2.f;
+            p.subZoneAgent[idx].inSubZone = aabbContains(zbox, pos_in_zone) ? 1 : 0;
+            p.subZoneAgent[idx].minDistToSubZone = distance(spawn_pt, zone_center);
+        }
         StandState st; st.cur = 0; st.tgt = 0; st.transition = 0;
         p.stand[idx] = st;
         MoveState ms; ms.newPos = p.pos[idx]; ms.newVel = v3(0, 0, 0); ms.maxVel = kMaxWalkVelocity;
@@ -380,6 +399,39 @@ MP_HD void zoneSystem(const Ctx &c, int w)
     } else if (num_a == 0 && num_b > 0) {
         if (zs.curControllingTeam != 1) {
             zs.curControllingTeam = 1; zs.isCaptured = 0; zs.stepsUntilPoint = kZonePointInterval;
+        }
+    }
+}
+
+// subzoneSystem (sim.cpp:1978-2043), all eight sub-zones of world w (SimFlags::SubZones).
+MP_HD void subzoneSystems(const Ctx &c, int w)
+{
+    const SimPtrs &p = c.p;
+    const MapConsts &mc = *c.mc;
+    const int base = w * kAgents;
+    for (int z = 0; z < kNumSubZones; z++) {
+        const ZOBB &sz = mc.subZones[z];
+        Quat to_zone = quatInv(angleAxis(sz.rotation, kUp()));
+        AABB zbox; zbox.pMin = rotateVec(to_zone, sz.pMin); zbox.pMax = rotateVec(to_zone, sz.pMax);
+        int num_a = 0, num_b = 0;
+        for (int i = 0; i < kAgents; i++) {
+            if (subZoneOf(p, base + i) != z) continue;
+            Vec3 pos = p.pos[base + i];
+            pos.z += kStandHeight / 2.f;
+            if (!aabbContains(zbox, rotateVec(to_zone, pos))) { p.subZoneAgent[base + i].inSubZone = 0; continue; }
+            p.subZoneAgent[base + i].inSubZone = 1;
+            p.subZoneAgent[base + i].minDistToSubZone = 0.f;
+            if (teamOf(i) == 0) num_a++; else num_b++;
+        }
+        SubZoneState &st = p.subZones[(size_t)w * kNumSubZones + z];
+        st.isContested = (num_a > 0 && num_b > 0) ? 1 : 0;
+        if (st.isContested || (num_a == 0 && num_b == 0)) {
+            st.curControllingTeam = -1;
+            st.isCaptured = 0;
+        } else if (num_a > 0 && num_b == 0) {
+            if (st.curControllingTeam != 0) { st.curControllingTeam = 0; st.isCaptured = 0; }
+        } else if (num_a == 0 && num_b > 0) {
+            if (st.curControllingTeam != 1) { st.curControllingTeam = 1; st.isCaptured = 0; }
         }
     }
 }
@@ -843,6 +895,62 @@ MP_HD void zoneRewardSystem(const Ctx &c, int w, int a)
     p.reward[idx] = reward;
 }
 
+// subzoneRewardSystem (sim.cpp:3734-3848): SimFlags::SubZones replaces zoneRewardSystem in the
+// Step graph (sim.cpp:5749-5766) -- the zone terms are taken against the agent's own sub-zone.
+MP_HD void subzoneRewardSystem(const Ctx &c, int w, int a)
+{
+    const SimPtrs &p = c.p;
+    const MapConsts &mc = *c.mc;
+    const int idx = w * kAgents + a;
+    CombatState &cs = p.combat[idx];
+    float reward = 0.f;
+    if (p.worldCurriculum[w] == 0) {
+        if (cs.landedShotOn != -1) reward += 0.5f;
+        else if (cs.firedShotT >= 0.f) reward -= 0.05f;
+        if (cs.reloadedFullMag) reward -= 0.5f;
+        p.reward[idx] = reward;
+        return;
+    }
+    const RewardHyperParams hp = p.rewardCoefs[idx];
+    reward -= hp.breadcrumbScale * p.crumbAgent[idx].totalPenalty;
+    if (cs.reloadedFullMag) reward -= 0.5f;
+    if (cs.successfulKill) reward += 3.f;
+    if (cs.landedShotOn != -1) reward += hp.shotScale * 1.f;
+    if (cs.wasKilled) reward -= 1.5f;
+    if (cs.wasShotCount > 0) reward -= hp.shotScale * 1.f;
+    uint32_t num_new_cells = p.exploreNew[idx];
+    p.exploreNew[idx] = 0;
+    if (num_new_cells > 0) reward += float(num_new_cells) * hp.exploreScale;
+    const int z = subZoneOf(p, idx);
+    const SubZoneState &st = p.subZones[(size_t)w * kNumSubZones + z];
+    SubZoneAgentState &sa = p.subZoneAgent[idx];
+    if (sa.inSubZone) {
+        reward += hp.inZoneScale;
+    } else {
+        const ZOBB &sz = mc.subZones[z];
+        Vec3 center = (sz.pMax + sz.pMin) / 2.f;
+        float dist = distance(center, p.pos[idx]);
+        if (dist < sa.minDistToSubZone) {
+            float zone_dist_scale = hp.zoneDistScale;
+            if (!cs.hasDiedDuringEpisode) zone_dist_scale *= 10.f;
+            reward += zone_dist_scale * (sa.minDistToSubZone - dist);
+            sa.minDistToSubZone = dist;
+        }
+    }
+    if (st.curControllingTeam != -1) {
+        if (st.curControllingTeam == teamOf(a)) reward += hp.zoneTeamCtrlScale;
+        else reward -= hp.zoneTeamCtrlScale;
+    }
+    if (p.alive[idx] == 0.f) {
+        cs.successfulKill = 0;
+        cs.landedShotOn = -1;
+        cs.wasKilled = 0;
+        cs.wasShotCount = 0;
+        cs.firedShotT = -FLT_MAX;
+    }
+    p.reward[idx] = reward;
+}
+
 // zoneCaptureDefendRewardSystem (sim.cpp:4089-4209): Task::ZoneCaptureDefend's per-agent reward
 // (goal-region progress of the agent's team, kills / hits, exploration, zone control for the
 // controlling team only, +-20 / -5 at the end of the match).
@@ -992,6 +1100,10 @@ MP_HD void initWorld(const Ctx &c, int w, bool triggered_reset)
     zs.earnedPoint = 0;
     zs.zoneStepsRemaining = kNumStepsPerZone;
     zs.stepsUntilPoint = kZonePointInterval;
+    for (int z = 0; z < kNumSubZones; z++) {            // sim.cpp:815-820 (whatever the flags)
+        SubZoneState &st = p.subZones[(size_t)w * kNumSubZones + z];
+        st.curControllingTeam = -1; st.isContested = 0; st.isCaptured = 0;
+    }
     if (c.cfg.taskCaptureDefend) zs.curZone = 3;       // sim.cpp:822-825 (after the draw: the RNG count is unchanged)
 
     // ---- resetPersistentEntities
@@ -1171,6 +1283,7 @@ MP_HD void stageWorld(const Ctx &c, int w)
         if (!(c.cfg.simFlags & kFlagNoRespawn)) spawnAgents(c, w, true);
         for (int i = 0; i < kAgents; i++) autoHealSystem(p, base + i);
         zoneSystem(c, w);
+        if (c.cfg.simFlags & kFlagSubZones) subzoneSystems(c, w);       // sim.cpp:5549-5555
         if (c.cfg.recordLog)
             for (int i = 0; i < kAgents; i++) recordAgent(c, w, i);
         breadcrumbSystems(c, w);
@@ -1181,6 +1294,7 @@ MP_HD void stageWorld(const Ctx &c, int w)
     for (int i = 0; i < kAgents; i++) {
         if (c.cfg.taskCaptureDefend) zoneCaptureDefendRewardSystem(c, w, i);
         else if (c.cfg.rewardFlank) flankRewardSystem(c, w, i);
+        else if (c.cfg.simFlags & kFlagSubZones) subzoneRewardSystem(c, w, i);
         else zoneRewardSystem(c, w, i);
     }
     teamAndFinalReward(c, w);

@@ -335,7 +335,7 @@ int mpenv_create(const mpenv_config *cfg, mpenv_handle **out)
     if (cfg->team_size != (uint32_t)kTeamSize) return fail(nullptr, MPENV_ERR_INVALID, "team_size must be 6");
     if (cfg->num_worlds == 0 || cfg->num_worlds > (1u << 22)) return fail(nullptr, MPENV_ERR_INVALID, "num_worlds out of range");
     const uint32_t unsupported = MPENV_FLAG_SPAWN_IN_MIDDLE | MPENV_FLAG_NAVMESH_SPAWN |
-        MPENV_FLAG_HARDCODED_SPAWNS | MPENV_FLAG_FULL_TEAM_POLICY | MPENV_FLAG_SUBZONES;
+        MPENV_FLAG_HARDCODED_SPAWNS | MPENV_FLAG_FULL_TEAM_POLICY;
     if (cfg->sim_flags & unsupported) return fail(nullptr, MPENV_ERR_INVALID, "unsupported sim_flags bit set");
 
     int dev_count = 0;
@@ -356,7 +356,8 @@ int mpenv_create(const mpenv_config *cfg, mpenv_handle **out)
     h->recordLog = cfg->record_log_path != nullptr;
     h->replayLog = cfg->replay_log_path != nullptr;
     h->cold = h->eventLog || h->recordLog || h->replayLog || cfg->curriculum_data_path != nullptr ||
-              cfg->train_flank != 0 || cfg->task_type == MPENV_TASK_ZONE_CAPTURE_DEFEND;
+              cfg->train_flank != 0 || cfg->task_type == MPENV_TASK_ZONE_CAPTURE_DEFEND ||
+              (cfg->sim_flags & MPENV_FLAG_SUBZONES) != 0;
     if (h->eventLog) h->eventDir = cfg->event_log_dir;
     if (h->recordLog) h->recordPath = cfg->record_log_path;
     if (h->replayLog) h->replayPath = cfg->replay_log_path;
@@ -371,6 +372,12 @@ int mpenv_create(const mpenv_config *cfg, mpenv_handle **out)
     if (!loadMapAssets(h->sceneDir, &h->assets, &err) || !fillMapConsts(h->assets, &h->hostConsts, &err)) {
         h->error = err;
         return bail(MPENV_ERR_IO);
+    }
+    if ((cfg->sim_flags & MPENV_FLAG_SUBZONES) && h->hostConsts.numZones < 3) {
+        // sub-zones 0 and 1 are zones 1 and 2 of the map (level_gen.cpp:283-293)
+        h->error = "SimFlags::SubZones needs a map with at least 3 zones";
+        g_create_error = h->error;
+        return bail(MPENV_ERR_INVALID);
     }
     if (cfg->task_type == MPENV_TASK_ZONE_CAPTURE_DEFEND && h->hostConsts.numZones < 4) {
         // initWorld pins the objective to zone 3 (sim.cpp:822-825)

@@ -41,6 +41,7 @@ inline const BufferDesc *bufferTable(int *count)
         MP_BUF(stand, sizeof(StandState), kPerAgent),
         MP_BUF(combat, sizeof(CombatState), kPerAgent),
         MP_BUF(crumbAgent, sizeof(CrumbAgentState), kPerAgent),
+        MP_BUF(subZoneAgent, sizeof(SubZoneAgentState), kPerAgent),
         MP_BUF(startPos, sizeof(Vec3), kPerAgent),
         MP_BUF(exploreGrid, 4 * kExploreGridW * kExploreGridW, kPerAgent),
         MP_BUF(exploreNew, 4, kPerAgent),
@@ -70,6 +71,7 @@ inline const BufferDesc *bufferTable(int *count)
         MP_BUF(matchResult, sizeof(MatchResult), kPerWorld),
         MP_BUF(resetFlag, 4, kPerWorld),
         MP_BUF(worldCurriculum, 4, kPerWorld),
+        MP_BUF(subZones, sizeof(SubZoneState) * kNumSubZones, kPerWorld),
         MP_BUF(ftGlobal, sizeof(FullTeamGlobalObs), kPerTeam),
         MP_BUF(ftPlayers, sizeof(FullTeamPlayerObs) * kTeamSize, kPerTeam),
         MP_BUF(ftEnemies, sizeof(FullTeamEnemyObs) * kTeamSize, kPerTeam),
@@ -218,6 +220,11 @@ inline void fillWorldState(const SimPtrs &p, mpenv_world_state *out)
     out->goal_team_step_rewards[1] = ws.goalTeamStepRewards[1];
     out->team_rewards[0] = ws.teamRewards[0];
     out->team_rewards[1] = ws.teamRewards[1];
+    for (int z = 0; z < kNumSubZones; z++) {
+        out->sub_zones[z][0] = p.subZones[z].curControllingTeam;
+        out->sub_zones[z][1] = p.subZones[z].isContested;
+        out->sub_zones[z][2] = p.subZones[z].isCaptured;
+    }
     memcpy(out->spawn_a_last_used, p.spawnUsage[0].a, sizeof(uint32_t) * kMaxSpawns);
     memcpy(out->spawn_b_last_used, p.spawnUsage[0].b, sizeof(uint32_t) * kMaxSpawns);
     memcpy(out->respawn_last_used, p.spawnUsage[0].respawn, sizeof(uint32_t) * kMaxSpawns);
@@ -258,6 +265,8 @@ inline void fillWorldState(const SimPtrs &p, mpenv_world_state *out)
         a.has_died = cs.hasDiedDuringEpisode;
         a.reloaded_full_mag = cs.reloadedFullMag;
         a.weapon_type = cs.weaponType;
+        a.in_sub_zone = p.subZoneAgent[i].inSubZone;
+        a.min_dist_to_sub_zone = p.subZoneAgent[i].minDistToSubZone;
         a.crumb_total_penalty = p.crumbAgent[i].totalPenalty;
         a.crumb_steps_since_new = p.crumbAgent[i].stepsSinceNew;
         a.crumb_last = -1;

@@ -175,6 +175,11 @@ __global__ void __launch_bounds__(128) k_world(KernelArgs ka)
             if (agent) autoHealSystem(p, base + lane);
             __syncwarp();
             zoneSystemCoop(c, w, lane, half, valid);
+            if (kCold && (c.cfg.simFlags & kFlagSubZones)) {           // sim.cpp:5549-5555
+                __syncwarp();
+                if (lead) subzoneSystems(c, w);
+                __syncwarp();
+            }
             if (kCold && c.cfg.recordLog && agent) recordAgent(c, w, lane);
             breadcrumbSystemsCoop(c, w, lane, half, valid);
         }
@@ -185,6 +190,7 @@ __global__ void __launch_bounds__(128) k_world(KernelArgs ka)
             exploreVisitedSystem(c, w, base + lane);
             if (kCold && c.cfg.taskCaptureDefend) zoneCaptureDefendRewardSystem(c, w, lane);
             else if (kCold && c.cfg.rewardFlank) flankRewardSystem(c, w, lane);
+            else if (kCold && (c.cfg.simFlags & kFlagSubZones)) subzoneRewardSystem(c, w, lane);
             else zoneRewardSystem(c, w, lane);
         }
         __syncwarp();

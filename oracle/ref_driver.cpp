@@ -612,6 +612,12 @@ int ref_get_world_state(void *h, uint32_t world, mpenv_world_state *out)
     const TeamRewardState &tr = ctx.singleton<TeamRewardState>();
     out->team_rewards[0] = tr.teamRewards[0];
     out->team_rewards[1] = tr.teamRewards[1];
+    for (int z = 0; z < 8; z++) {
+        const SubZone &sz = ctx.get<SubZone>(sim.subZones[z]);
+        out->sub_zones[z][0] = sz.curControllingTeam;
+        out->sub_zones[z][1] = sz.isContested;
+        out->sub_zones[z][2] = sz.isCaptured;
+    }
 
     const SpawnUsageCounter &su = ctx.singleton<SpawnUsageCounter>();
     memcpy(out->spawn_a_last_used, su.initASpawnsLastUsedTick, sizeof(uint32_t) * 128);
@@ -674,6 +680,8 @@ int ref_get_world_state(void *h, uint32_t world, mpenv_world_state *out)
         a.has_died = cs.hasDiedDuringEpisode;
         a.reloaded_full_mag = cs.reloadedFullMag;
         a.weapon_type = cs.weaponType;
+        a.in_sub_zone = cs.inSubZone;
+        a.min_dist_to_sub_zone = cs.minDistToSubZone;
         const BreadcrumbAgentState &bs = ctx.get<BreadcrumbAgentState>(e);
         a.crumb_total_penalty = bs.totalPenalty;
         a.crumb_steps_since_new = bs.stepsSinceLastNewBreadcrumb;

@@ -48,6 +48,7 @@ class AgentState(C.Structure):
         ("crumb_last", C.c_int32), ("start_pos", C.c_float * 3), ("explore_new_cells", C.c_uint32),
         ("can_see", C.c_int32 * 6), ("team", C.c_int32), ("team_offset", C.c_int32),
         ("policy", C.c_int32), ("reward_coefs", C.c_float * 9),
+        ("in_sub_zone", C.c_int32), ("min_dist_to_sub_zone", C.c_float),
     ]
 
 
@@ -72,6 +73,7 @@ class WorldState(C.Structure):
         ("filters_last_matched_step", C.c_int32 * 2),
         ("goal_min_dist", C.c_float * 2), ("goal_team_step_rewards", C.c_float * 2),
         ("team_rewards", C.c_float * 2),
+        ("sub_zones", (C.c_int32 * 3) * 8),
         ("spawn_a_last_used", C.c_uint32 * 128), ("spawn_b_last_used", C.c_uint32 * 128),
         ("respawn_last_used", C.c_uint32 * 128),
         ("num_breadcrumbs", C.c_int32), ("breadcrumbs", CrumbState * 192),

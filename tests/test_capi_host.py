@@ -87,7 +87,7 @@ def test_create_argument_errors(lib):
         S.MpenvConfig(0, 4, 10, 0, 0, 1, 6, 0, 1, scene, 0, 1, None, None, None, None, 0),            # TDM: unsupported task
         S.MpenvConfig(0, 4, 10, 0, 0, 2, 4, 0, 1, scene, 0, 1, None, None, None, None, 0),            # team size
         S.MpenvConfig(0, 0, 10, 0, 0, 2, 6, 0, 1, scene, 0, 1, None, None, None, None, 0),            # zero worlds
-        S.MpenvConfig(0, 4, 10, 0, 1 << 11, 2, 6, 0, 1, scene, 0, 1, None, None, None, None, 0),      # SubZones flag
+        S.MpenvConfig(0, 4, 10, 0, 1 << 6, 2, 6, 0, 1, scene, 0, 1, None, None, None, None, 0),       # HardcodedSpawns flag
     ]
     for cfg in bad:
         assert lib.mpenv_create(C.byref(cfg), C.byref(h)) == -1           # MPENV_ERR_INVALID

@@ -379,3 +379,10 @@ def test_zone_capture_defend_gpu(tmp_path, variant, flags):
 def test_zone_capture_defend_needs_four_zones():
     with pytest.raises(RuntimeError, match="at least 4 zones"):
         S.GpuSim(2, task=4)
+
+
+def test_subzones_gpu():
+    """SimFlags::SubZones (SURVEY 8f-4): subzoneSystem + subzoneRewardSystem, agents re-assigned to the
+    sub-zones they stand in through the live policy tensor -- see test_hostsim_parity.py."""
+    from test_hostsim_parity import subzones_rollout
+    subzones_rollout(lambda W, f: S.GpuSim(W, sim_flags=f, auto_reset=True), assert_same)

@@ -197,3 +197,55 @@ def test_zone_capture_defend(built, tmp_path, variant, flags):
         str(tmp_path / "four_zones"), variant, flags, assert_same)
     expect = {"north": (False, 8), "south": (True, 1), "sky": (False, 0)}[variant]
     assert expect in outcomes, f"{variant}: outcomes {outcomes}"
+
+
+def subzones_rollout(make_ours, assert_same_fn, steps=240):
+    """SimFlags::SubZones (SURVEY 8f-4; sim.cpp:1978-2043 subzoneSystem, 3734-3848 subzoneRewardSystem,
+    utils.cpp:906-926, level_gen.cpp:279-322): every agent's sub-zone is its policy id (clamped to
+    0..7), so the policy-assignment tensor spreads the agents over all eight sub-zones."""
+    W = 4
+    flags = 1 << 11
+    ours = make_ours(W, flags)
+    orc = S.Oracle(W, sim_flags=flags, auto_reset=True, det=True)
+    try:
+        pol = (np.arange(W * 12, dtype=np.int32) % 10 - 1).reshape(-1, 1)     # -1 .. 8: both clamps
+        pol[pol == -1] = 0        # policy -1 is the scripted bot (another row of 8f): keep learned agents
+        for sim in (ours, orc):
+            sim.set_export("agent_policy", pol)
+        ours.init(); orc.init()
+        assert_same_fn(ours, orc, W, "init")
+        # sub-zone boxes as level_gen.cpp:279-322 lays them out on simple_map (zones 1, 2 + six constants)
+        boxes = [S.FOUR_ZONES[1][:6], S.FOUR_ZONES[2][:6], (-950, -500, 0, -50, 500, 1000), (50, -500, 0, 950, 500, 1000),
+                 (-1000, -1650, 0, -50, -600, 1000), (50, -1650, 0, 1000, -600, 1000),
+                 (-1000, 600, 0, -50, 1650, 1000), (1000, 600, 0, 50, 1650, 1000)]
+        inside = controlled = 0
+        for s in range(steps):
+            d, a = S.seek_policy(orc, s, W)
+            if s in (80, 160):
+                # re-assign every agent to a sub-zone it is standing in (if any): the policy tensor is a
+                # live input, so containment, control and contest all get exercised from here on
+                pol = orc.export("agent_policy").copy()
+                for w in range(W):
+                    for i, ag in enumerate(orc.world_state(w)["agents"]):
+                        x, y, z = ag["pos"][0], ag["pos"][1], ag["pos"][2] + 25.0
+                        for k, b in enumerate(boxes):
+                            if b[0] <= x <= b[3] and b[1] <= y <= b[4] and b[2] <= z <= b[5]:
+                                pol[w * 12 + i, 0] = k
+                                break
+                for sim in (ours, orc):
+                    sim.set_export("agent_policy", pol)
+            for sim in (ours, orc):
+                sim.set_actions(d, a); sim.step()
+            if s % 20 == 19 or s in (80, 81, 160, 161):
+                assert_same_fn(ours, orc, W, f"step {s}")
+            for w in range(W):
+                st = orc.world_state(w)
+                inside += sum(ag["in_sub_zone"] for ag in st["agents"])
+                controlled += int((np.asarray(st["sub_zones"])[:, 0] >= 0).sum())
+        assert inside > 0 and controlled > 0, "no agent ever stood in its sub-zone: the system was not exercised"
+    finally:
+        ours.close(); orc.close()
+
+
+def test_subzones(built):
+    subzones_rollout(lambda W, f: S.HostSim(W, sim_flags=f, auto_reset=True), assert_same)
