@@ -13,6 +13,7 @@
 
 #include "step_kernels.cuh"
 #include "lidar_stream.cuh"
+#include "lidar_packet.cuh"
 #include "assets.h"
 #include "sim_layout.h"
 #include "../../include/mpenv.h"
@@ -56,6 +57,9 @@ struct mpenv_handle {
     bool poolLidar = false;                  // warp-pooled ray engine (ray_fast.cuh): lidar task stream
     size_t lidarPoolSmem = 0;
     int gridLidarPool = 0;
+    bool packetLidar = false;                // packet traversal (lidar_packet.cuh)
+    size_t lidarPacketSmem = 0;
+    int gridLidarPacket = 0;
     bool poolLos = false;
     size_t losPoolSmem = 0;
     int gridLosPool = 0;
@@ -110,6 +114,23 @@ int fail(mpenv_handle *h, int code, const std::string &msg)
     return code;
 }
 
+// Depth of the 4-wide tree (root = 1): bounds the packet kernel's shared stack.
+int bvhDepth(const std::vector<BVHNode> &nodes)
+{
+    int best = 0;
+    std::vector<std::pair<int, int>> todo(1, { 0, 1 });
+    while (!todo.empty()) {
+        const auto [n, d] = todo.back();
+        todo.pop_back();
+        if (d > best) best = d;
+        for (int k = 0; k < 4; k++) {
+            const int32_t ch = nodes[(size_t)n].children[k];
+            if (ch != kBVHSentinel && !(ch & 0x80000000)) todo.push_back({ (int)ch, d + 1 });
+        }
+    }
+    return best;
+}
+
 template <typename K>
 int gridFor(mpenv_handle *h, K kernel, int block, size_t smem, long long items)
 {
@@ -124,7 +145,9 @@ int gridFor(mpenv_handle *h, K kernel, int block, size_t smem, long long items)
 
 void launchLidar(mpenv_handle *h, cudaStream_t s)
 {
-    if (h->poolLidar)
+    if (h->packetLidar)
+        k_lidar_packet<<<h->gridLidarPacket, kPacketWarpsPerCTA * 32, h->lidarPacketSmem, s>>>(h->ka);
+    else if (h->poolLidar)
         k_lidar_stream<MPENV_STREAM_LEAF, MPENV_STREAM_REFILL><<<h->gridLidarPool, kStreamWarpsPerCTA * 32, h->lidarPoolSmem, s>>>(h->ka);
     else k_lidar<<<h->gridLidar, 160, h->bvhSmemBytes, s>>>(h->ka);
 }
@@ -555,6 +578,16 @@ int mpenv_create(const mpenv_config *cfg, mpenv_handle **out)
     if (h->poolLos) {
         MP_CREATE(cudaFuncSetAttribute(k_los_pool<10, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->losPoolSmem));
         h->gridLosPool = gridFor(h, k_los_pool<10, 8>, kLosWarpsPerCTA * 32, h->losPoolSmem, W * 32);
+    }
+    {
+        const char *lm = getenv("MPENV_LIDAR");
+        h->lidarPacketSmem = lidarPacketSmemBytes(ka.ctx.bvh.numNodes, ka.ctx.bvh.numTris);
+        h->packetLidar = !legacy && !(lm && strcmp(lm, "stream") == 0) && h->lidarPacketSmem <= 100 * 1024 &&
+                         3 * bvhDepth(h->assets.nodes) + 1 <= kPacketStack;
+        if (h->packetLidar) {
+            MP_CREATE(cudaFuncSetAttribute(k_lidar_packet, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->lidarPacketSmem));
+            h->gridLidarPacket = gridFor(h, k_lidar_packet, kPacketWarpsPerCTA * 32, h->lidarPacketSmem, (N / 2) * 32);
+        }
     }
     if (h->poolLidar) {
         auto kern = k_lidar_stream<MPENV_STREAM_LEAF, MPENV_STREAM_REFILL>;
