@@ -12,7 +12,6 @@
 #include <nvtx3/nvToolsExt.h>
 
 #include "step_kernels.cuh"
-#include "lidar_stream.cuh"
 #include "lidar_packet.cuh"
 #include "assets.h"
 #include "sim_layout.h"
@@ -54,9 +53,6 @@ struct mpenv_handle {
     char *snapshot = nullptr;
     size_t snapshotBytes = 0;
     bool copyInFlight = false;
-    bool poolLidar = false;                  // warp-pooled ray engine (ray_fast.cuh): lidar task stream
-    size_t lidarPoolSmem = 0;
-    int gridLidarPool = 0;
     bool packetLidar = false;                // packet traversal (lidar_packet.cuh)
     size_t lidarPacketSmem = 0;
     int gridLidarPacket = 0;
@@ -147,8 +143,6 @@ void launchLidar(mpenv_handle *h, cudaStream_t s)
 {
     if (h->packetLidar)
         k_lidar_packet<<<h->gridLidarPacket, kPacketWarpsPerCTA * 32, h->lidarPacketSmem, s>>>(h->ka);
-    else if (h->poolLidar)
-        k_lidar_stream<MPENV_STREAM_LEAF, MPENV_STREAM_REFILL><<<h->gridLidarPool, kStreamWarpsPerCTA * 32, h->lidarPoolSmem, s>>>(h->ka);
     else k_lidar<<<h->gridLidar, 160, h->bvhSmemBytes, s>>>(h->ka);
 }
 
@@ -571,8 +565,6 @@ int mpenv_create(const mpenv_config *cfg, mpenv_handle **out)
     // that path so that the tests can cover it on simple_map.
     const char *kmode = getenv("MPENV_KERNELS");
     const bool legacy = kmode && strcmp(kmode, "legacy") == 0;
-    h->lidarPoolSmem = lidarStreamSmemBytes(ka.ctx.bvh.numNodes, ka.ctx.bvh.numTris);
-    h->poolLidar = !legacy && h->lidarPoolSmem <= 220 * 1024;
     h->losPoolSmem = losPoolSmemBytes(ka.ctx.bvh.numNodes, ka.ctx.bvh.numTris);
     h->poolLos = !legacy && h->losPoolSmem <= 200 * 1024;
     if (h->poolLos) {
@@ -580,21 +572,16 @@ int mpenv_create(const mpenv_config *cfg, mpenv_handle **out)
         h->gridLosPool = gridFor(h, k_los_pool<10, 8>, kLosWarpsPerCTA * 32, h->losPoolSmem, W * 32);
     }
     {
-        const char *lm = getenv("MPENV_LIDAR");
+        // two CTAs per SM: each may use half of the 227 KB; the shared stack holds <= 3 pending
+        // children per tree level
         h->lidarPacketSmem = lidarPacketSmemBytes(ka.ctx.bvh.numNodes, ka.ctx.bvh.numTris);
-        h->packetLidar = !legacy && !(lm && strcmp(lm, "stream") == 0) && h->lidarPacketSmem <= 100 * 1024 &&
+        h->packetLidar = !legacy && h->lidarPacketSmem <= 110 * 1024 &&
                          3 * bvhDepth(h->assets.nodes) + 1 <= kPacketStack;
         if (h->packetLidar) {
             MP_CREATE(cudaFuncSetAttribute(k_lidar_packet, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->lidarPacketSmem));
             h->gridLidarPacket = gridFor(h, k_lidar_packet, kPacketWarpsPerCTA * 32, h->lidarPacketSmem, (N / 2) * 32);
         }
     }
-    if (h->poolLidar) {
-        auto kern = k_lidar_stream<MPENV_STREAM_LEAF, MPENV_STREAM_REFILL>;
-        MP_CREATE(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->lidarPoolSmem));
-        h->gridLidarPool = gridFor(h, kern, kStreamWarpsPerCTA * 32, h->lidarPoolSmem, (N / 2) * 32);
-    }
-
     // Sim::Sim for every world (sim.cpp:5850-5980)
     k_ctor<<<h->gridSmall, 128, 0, h->stream>>>(ka);
     MP_CREATE(cudaGetLastError());

@@ -10,24 +10,12 @@
 namespace mpenv {
 
 // ------------------------------------------------------------------- lidar
-// pvpLidarSystem (sim.cpp:3324-3506): the kernel is k_lidar_stream (lidar_stream.cuh).
+// pvpLidarSystem (sim.cpp:3324-3506): the kernel is k_lidar_packet (lidar_packet.cuh).
 // A task is TWO agents of one world = 160 rays: 2 x (2 heights x 32 forward columns +
 // 2 heights x 8 rear columns).  The two heights share their directions, so a task has
 // 80 unique directions and 4 origins.
 constexpr int kLidarRaysPerAgent = kFwdLidarH * kFwdLidarW + kRearLidarH * kRearLidarW;   // 80
-constexpr int kLidarDirsPerAgent = kFwdLidarW + kRearLidarW;                              // 40
 constexpr int kLidarTaskRays = 2 * kLidarRaysPerAgent;                                    // 160
-
-// ray index within a task -> (agent 0/1, ray 0..79, height, direction slot)
-__device__ __forceinline__ void lidarDecode(int ray, int *agent, int *rr, int *h, int *dir)
-{
-    const int ag = ray >= kLidarRaysPerAgent ? 1 : 0;
-    const int r = ray - ag * kLidarRaysPerAgent;
-    int hh, d;
-    if (r < kFwdLidarH * kFwdLidarW) { hh = r >> 5; d = r & 31; }
-    else { const int r2 = r - kFwdLidarH * kFwdLidarW; hh = r2 >> 3; d = kFwdLidarW + (r2 & 7); }
-    *agent = ag; *rr = r; *h = hh; *dir = ag * kLidarDirsPerAgent + d;
-}
 
 // --------------------------------------------------------------------- LOS
 // opponentsWriteVisibilitySystem (sim.cpp:2526-2560) + isAgentVisible

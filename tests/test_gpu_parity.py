@@ -323,10 +323,10 @@ def test_pipelined_readback_equals_sync_read():
 
 
 @pytest.mark.parametrize("W", [1, 3, 37, 700])
-def test_lidar_stream_vs_oracle(W):
-    """k_lidar_stream (two resident tasks per warp, tasks drawn from a device-wide counter,
-    lidar_stream.cuh) against the oracle: warps with no task, one task, an odd number of
-    tasks and a long stream of them."""
+def test_lidar_packets_vs_oracle(W):
+    """k_lidar_packet (five 32-ray packets per 2-agent task, tasks drawn from a device-wide counter,
+    lidar_packet.cuh) against the oracle: warps with no task, one task, an odd number of
+    tasks and many of them."""
     gpu = S.GpuSim(W, auto_reset=True, full_team=False)
     orc = S.Oracle(W, auto_reset=True, det=True, num_threads=0)
     try:
