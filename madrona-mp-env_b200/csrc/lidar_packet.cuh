@@ -62,10 +62,12 @@ __device__ __forceinline__ float tracePacket(const char *smem, const FastBVH &bv
         const uint32_t meta = reinterpret_cast<const uint32_t *>(nd)[3];
         const int4 ch = reinterpret_cast<const int4 *>(nd)[2];
         const int32_t child[4] = { ch.x, ch.y, ch.z, ch.w };
+        // a lane that does not visit this node compares against -1: no child is ever hit
+        float t_eff = active ? t_max : -1.f;
 #pragma unroll
         for (int i = 0; i < 4; i++) {
             // the lane's own test at this child's turn (t_max may have shrunk at an earlier leaf)
-            const bool hit = active && tn[i] <= t_max;
+            const bool hit = tn[i] <= t_eff;
             const unsigned m = __ballot_sync(0xFFFFFFFFu, hit);
             if (m == 0) continue;
             if ((meta >> i) & 1u) {
@@ -78,6 +80,7 @@ __device__ __forceinline__ float tracePacket(const char *smem, const FastBVH &bv
                         float t;
                         if (rayTriangleFast(tri + k, tc, t_max, &t)) t_max = t;
                     }
+                    t_eff = t_max;
                 }
             } else {
                 if (lane == 0) stack[sp] = make_uint2((uint32_t)child[i], m);
