@@ -328,13 +328,19 @@ def run_e2e(args, torch, dist, lib, h, X, all_d, all_a, rank, world, W, N, dev):
     dsts = (C.c_void_p * len(sizes))(*[base.value + x for x in offs])
     hs = C.c_void_p(lib.mpenv_stream(h))
 
+    lib.mpenv_snapshot_tensors_async.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32]
+    lib.mpenv_read_snapshot_async.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32]
+
     def e2e_step(i):
-        # host actions in, step, host observations out; the read-back of step i overlaps step i+1
+        # host actions in, step, host observations out.  The device snapshot of step i is queued behind
+        # the step at once (double-buffered), so it is taken while step i-1 is still crossing PCIe; its
+        # own transfer starts as soon as the host buffers are free again.
         lib.mpenv_write_tensor_async(h, X.EXPORT_IDS["pvp_discrete_action"], hd[i % 8].data_ptr(), hd[0].numel() * 4)
         lib.mpenv_write_tensor_async(h, X.EXPORT_IDS["pvp_discrete_aim_action"], ha[i % 8].data_ptr(), ha[0].numel() * 4)
         lib.mpenv_step_async(h, hs)
+        assert lib.mpenv_snapshot_tensors_async(h, ids, len(sizes)) == 0
         lib.mpenv_read_wait(h)              # step i-1's tensors are now on the host
-        assert lib.mpenv_read_tensors_pipelined(h, ids, dsts, len(sizes)) == 0
+        assert lib.mpenv_read_snapshot_async(h, dsts, len(sizes)) == 0
     k2 = max(5, min(args.steps, 50))
     for i in range(3):
         e2e_step(i)
@@ -382,8 +388,8 @@ def run_e2e(args, torch, dist, lib, h, X, all_d, all_a, rank, world, W, N, dev):
             "frac_of_ceiling": round(got_gbs / ceil_gbs, 3),
             "ceiling_agent_steps_per_s": round(world * ceil_gbs * 1e9 / (d2h / N), 1),
             "note": "C ABI, pinned host buffers (mpenv_host_alloc), every step: mpenv_write_tensor_async(actions) + "
-                    "mpenv_step_async + mpenv_read_tensors_pipelined(18 output tensors, device snapshot then D2H on a "
-                    "copy stream, overlapping the next step); host wall clock around k steps incl. the last read. "
+                    "mpenv_step_async + mpenv_snapshot_tensors_async + mpenv_read_snapshot_async (18 output tensors, "
+                    "double-buffered device snapshot, D2H on a copy stream overlapping the next step); host wall clock around k steps incl. the last read. "
                     "pcie_gbs = pinned D2H rate per rank of the same bytes with all ranks copying at once and no "
                     "kernels running; the e2e number is bound by it, not by the kernels"}
 

@@ -180,6 +180,14 @@ int mpenv_read_tensor_async(mpenv_handle *h, uint32_t export_id, void *host_dst,
  * mpenv_read_wait() returns; a new call first waits (stream-ordered) for the
  * previous transfer.  Pinned host memory required for real overlap. */
 int mpenv_read_tensors_pipelined(mpenv_handle *h, const uint32_t *export_ids, void *const *host_dst, uint32_t n);
+/* The two halves of mpenv_read_tensors_pipelined, for a host loop that reuses ONE set of host
+ * buffers: the snapshots are double-buffered on the device, so the snapshot of step t+1 can be
+ * queued (right after mpenv_step_async) while step t's transfer is still running; the transfer
+ * of step t+1 is then started, with mpenv_read_snapshot_async, once the consumer is done with the
+ * host buffers (after mpenv_read_wait).  Keeps the PCIe link busy back to back.
+ * mpenv_read_snapshot_async reads the tensors of the latest snapshot, in its order (n must match). */
+int mpenv_snapshot_tensors_async(mpenv_handle *h, const uint32_t *export_ids, uint32_t n);
+int mpenv_read_snapshot_async(mpenv_handle *h, void *const *host_dst, uint32_t n);
 int mpenv_read_wait(mpenv_handle *h);
 int mpenv_host_alloc(uint64_t bytes, void **out);
 void mpenv_host_free(void *p);

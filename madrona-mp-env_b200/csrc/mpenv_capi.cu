@@ -49,9 +49,14 @@ struct mpenv_handle {
     bool fullTeam = false;
     // pipelined host read-back (mpenv_read_tensors_pipelined)
     cudaStream_t copyStream = nullptr;
-    cudaEvent_t evSnap = nullptr, evCopied = nullptr;
-    char *snapshot = nullptr;
+    cudaEvent_t evSnap[2] = { nullptr, nullptr }, evRead[2] = { nullptr, nullptr }, evCopied = nullptr;
+    char *snapshot[2] = { nullptr, nullptr };    // double-buffered: snapshot t+1 is taken while t goes to the host
     size_t snapshotBytes = 0;
+    int snapNext = 0;                            // buffer the next snapshot goes into
+    int snapReady = -1;                          // buffer holding a snapshot that has not been read yet
+    uint32_t snapIds[64];
+    uint32_t snapCount = 0;
+    bool snapRead[2] = { false, false };         // a D2H from this buffer has been enqueued (evRead valid)
     bool copyInFlight = false;
     bool packetLidar = false;                // packet traversal (lidar_packet.cuh)
     size_t lidarPacketSmem = 0;
@@ -336,9 +341,12 @@ void mpenv_destroy(mpenv_handle *h)
     for (void *p : { (void *)h->hostEvTotals, (void *)h->hostEvents, (void *)h->hostSnaps, (void *)h->hostRecord,
                      (void *)h->hostReplay }) if (p) cudaFreeHost(p);
     if (h->copyStream) { cudaStreamSynchronize(h->copyStream); cudaStreamDestroy(h->copyStream); }
-    if (h->evSnap) cudaEventDestroy(h->evSnap);
+    for (int k = 0; k < 2; k++) {
+        if (h->evSnap[k]) cudaEventDestroy(h->evSnap[k]);
+        if (h->evRead[k]) cudaEventDestroy(h->evRead[k]);
+        if (h->snapshot[k]) cudaFree(h->snapshot[k]);
+    }
     if (h->evCopied) cudaEventDestroy(h->evCopied);
-    if (h->snapshot) cudaFree(h->snapshot);
     if (h->stream) cudaStreamDestroy(h->stream);
     delete h;
 }
@@ -787,48 +795,85 @@ int mpenv_read_tensor_async(mpenv_handle *h, uint32_t export_id, void *host_dst,
     return MPENV_OK;
 }
 
-int mpenv_read_tensors_pipelined(mpenv_handle *h, const uint32_t *export_ids, void *const *host_dst, uint32_t n)
+int mpenv_snapshot_tensors_async(mpenv_handle *h, const uint32_t *export_ids, uint32_t n)
 {
-    if (!h || !export_ids || !host_dst || n == 0 || n > 64) return MPENV_ERR_INVALID;
-    NvtxRange nvtx("mpenv_read_tensors_pipelined (snapshot + D2H)");
+    if (!h || !export_ids || n == 0 || n > 64) return MPENV_ERR_INVALID;
+    NvtxRange nvtx("mpenv_snapshot_tensors_async");
     MP_CUDA(h, cudaSetDevice(h->device));
     mpenv_tensor_desc d[64];
     size_t total = 0;
     for (uint32_t i = 0; i < n; i++) {
         int rc = mpenv_tensor(h, export_ids[i], &d[i]);
         if (rc != MPENV_OK) return rc;
-        if (!host_dst[i]) return fail(h, MPENV_ERR_INVALID, "mpenv_read_tensors_pipelined: null host buffer");
         total += (tensorBytes(d[i]) + 255) & ~(size_t)255;
     }
     if (!h->copyStream) {
         MP_CUDA(h, cudaStreamCreateWithFlags(&h->copyStream, cudaStreamNonBlocking));
-        MP_CUDA(h, cudaEventCreateWithFlags(&h->evSnap, cudaEventDisableTiming));
+        for (int k = 0; k < 2; k++) {
+            MP_CUDA(h, cudaEventCreateWithFlags(&h->evSnap[k], cudaEventDisableTiming));
+            MP_CUDA(h, cudaEventCreateWithFlags(&h->evRead[k], cudaEventDisableTiming));
+        }
         MP_CUDA(h, cudaEventCreateWithFlags(&h->evCopied, cudaEventDisableTiming));
     }
     if (total > h->snapshotBytes) {
         MP_CUDA(h, cudaStreamSynchronize(h->copyStream));
-        if (h->snapshot) cudaFree(h->snapshot);
-        h->snapshot = nullptr; h->snapshotBytes = 0;
-        MP_CUDA(h, cudaMalloc((void **)&h->snapshot, total));
+        for (int k = 0; k < 2; k++) {
+            if (h->snapshot[k]) cudaFree(h->snapshot[k]);
+            h->snapshot[k] = nullptr;
+            h->snapRead[k] = false;
+        }
+        h->snapshotBytes = 0;
+        for (int k = 0; k < 2; k++) MP_CUDA(h, cudaMalloc((void **)&h->snapshot[k], total));
         h->snapshotBytes = total;
     }
-    // the snapshot may not be overwritten before the previous transfer has left it
-    if (h->copyInFlight) MP_CUDA(h, cudaStreamWaitEvent(h->stream, h->evCopied, 0));
+    const int b = h->snapNext;
+    // this buffer may not be overwritten before the transfer that last read it has left it
+    if (h->snapRead[b]) MP_CUDA(h, cudaStreamWaitEvent(h->stream, h->evRead[b], 0));
     size_t off = 0;
     for (uint32_t i = 0; i < n; i++) {
-        MP_CUDA(h, cudaMemcpyAsync(h->snapshot + off, d[i].dev_ptr, tensorBytes(d[i]), cudaMemcpyDeviceToDevice, h->stream));
+        MP_CUDA(h, cudaMemcpyAsync(h->snapshot[b] + off, d[i].dev_ptr, tensorBytes(d[i]), cudaMemcpyDeviceToDevice, h->stream));
         off += (tensorBytes(d[i]) + 255) & ~(size_t)255;
+        h->snapIds[i] = export_ids[i];
     }
-    MP_CUDA(h, cudaEventRecord(h->evSnap, h->stream));
-    MP_CUDA(h, cudaStreamWaitEvent(h->copyStream, h->evSnap, 0));
-    off = 0;
+    h->snapCount = n;
+    MP_CUDA(h, cudaEventRecord(h->evSnap[b], h->stream));
+    h->snapReady = b;
+    h->snapNext = b ^ 1;
+    return MPENV_OK;
+}
+
+int mpenv_read_snapshot_async(mpenv_handle *h, void *const *host_dst, uint32_t n)
+{
+    if (!h || !host_dst || n == 0 || n > 64) return MPENV_ERR_INVALID;
+    if (h->snapReady < 0 || n != h->snapCount)
+        return fail(h, MPENV_ERR_INVALID, "mpenv_read_snapshot_async: no snapshot of that many tensors is pending");
+    NvtxRange nvtx("mpenv_read_snapshot_async (D2H)");
+    MP_CUDA(h, cudaSetDevice(h->device));
+    const int b = h->snapReady;
+    MP_CUDA(h, cudaStreamWaitEvent(h->copyStream, h->evSnap[b], 0));
+    size_t off = 0;
     for (uint32_t i = 0; i < n; i++) {
-        MP_CUDA(h, cudaMemcpyAsync(host_dst[i], h->snapshot + off, tensorBytes(d[i]), cudaMemcpyDeviceToHost, h->copyStream));
-        off += (tensorBytes(d[i]) + 255) & ~(size_t)255;
+        if (!host_dst[i]) return fail(h, MPENV_ERR_INVALID, "mpenv_read_snapshot_async: null host buffer");
+        mpenv_tensor_desc d;
+        int rc = mpenv_tensor(h, h->snapIds[i], &d);
+        if (rc != MPENV_OK) return rc;
+        MP_CUDA(h, cudaMemcpyAsync(host_dst[i], h->snapshot[b] + off, tensorBytes(d), cudaMemcpyDeviceToHost, h->copyStream));
+        off += (tensorBytes(d) + 255) & ~(size_t)255;
     }
+    MP_CUDA(h, cudaEventRecord(h->evRead[b], h->copyStream));
     MP_CUDA(h, cudaEventRecord(h->evCopied, h->copyStream));
+    h->snapRead[b] = true;
+    h->snapReady = -1;
     h->copyInFlight = true;
     return MPENV_OK;
+}
+
+int mpenv_read_tensors_pipelined(mpenv_handle *h, const uint32_t *export_ids, void *const *host_dst, uint32_t n)
+{
+    if (!h || !export_ids || !host_dst || n == 0 || n > 64) return MPENV_ERR_INVALID;
+    NvtxRange nvtx("mpenv_read_tensors_pipelined (snapshot + D2H)");
+    int rc = mpenv_snapshot_tensors_async(h, export_ids, n);
+    return rc != MPENV_OK ? rc : mpenv_read_snapshot_async(h, host_dst, n);
 }
 
 int mpenv_read_wait(mpenv_handle *h)

@@ -386,3 +386,44 @@ def test_subzones_gpu():
     sub-zones they stand in through the live policy tensor -- see test_hostsim_parity.py."""
     from test_hostsim_parity import subzones_rollout
     subzones_rollout(lambda W, f: S.GpuSim(W, sim_flags=f, auto_reset=True), assert_same)
+
+
+def test_double_buffered_snapshots():
+    """mpenv_snapshot_tensors_async / mpenv_read_snapshot_async in the bench's order: the snapshot of
+    step s is queued while the transfer of step s-1 may still be running, with ONE set of host buffers."""
+    import ctypes as C
+    W = 16
+    a_, b_ = S.GpuSim(W, auto_reset=True), S.GpuSim(W, auto_reset=True)
+    try:
+        L, h = a_.lib, a_.h
+        L.mpenv_snapshot_tensors_async.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32]
+        L.mpenv_read_snapshot_async.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32]
+        L.mpenv_read_wait.argtypes = [C.c_void_p]
+        L.mpenv_stream.restype = C.c_void_p
+        L.mpenv_stream.argtypes = [C.c_void_p]
+        names = ["self_obs", "fwd_lidar", "opponent_last_known_obs", "reward", "match_result"]
+        bufs = {n: np.zeros((S.rows_of(S.EXPORT_SHAPES[n][0], W), S.EXPORT_SHAPES[n][1]), S.EXPORT_SHAPES[n][2])
+                for n in names}
+        ids = (C.c_uint32 * len(names))(*[S.EXPORT_IDS[n] for n in names])
+        dst = (C.c_void_p * len(names))(*[bufs[n].ctypes.data for n in names])
+        a_.init(); b_.init()
+        prev = None
+        for s in range(14):
+            d, act = S.seek_policy(b_, s, W)
+            a_.set_actions(d, act); b_.set_actions(d, act)
+            assert L.mpenv_step_async(h, C.c_void_p(L.mpenv_stream(h))) == 0
+            assert L.mpenv_snapshot_tensors_async(h, ids, len(names)) == 0
+            assert L.mpenv_read_wait(h) == 0
+            if prev is not None:          # host buffers hold step s-1 although step s and its snapshot are queued
+                for n in names:
+                    assert np.array_equal(bufs[n].view(np.int32), prev[n].view(np.int32)), (s, n)
+            assert L.mpenv_read_snapshot_async(h, dst, len(names)) == 0
+            b_.step()
+            prev = {n: b_.export(n) for n in names}
+        assert L.mpenv_read_wait(h) == 0
+        for n in names:
+            assert np.array_equal(bufs[n].view(np.int32), prev[n].view(np.int32)), n
+        # a read without a pending snapshot is an error, not a stale copy
+        assert L.mpenv_read_snapshot_async(h, dst, len(names)) != 0
+    finally:
+        a_.close(); b_.close()
