@@ -55,8 +55,10 @@ def random_policy(sim, s, W):
 
 
 def test_random_actions_parity_run(built):
-    """BASELINE.json configs[0]: headless CPU run, 32 worlds, random actions, 1000 steps."""
-    rollout(32, 1000, random_policy, check_every=100)
+    """BASELINE.json configs[0] at its full length (random actions, 1000 steps) on 12 worlds: the stage
+    functions run single-threaded on the host; the 32-world run is the GPU test's
+    (test_gpu_parity.py::test_random_actions_32_worlds_bit_exact)."""
+    rollout(12, 1000, random_policy, check_every=100)
 
 
 def test_combat_policy(built):
