@@ -236,6 +236,10 @@ int mpenv_set_replay_log(mpenv_handle *h, const void *step_logs, uint64_t bytes)
 int mpenv_get_world_state(mpenv_handle *h, uint32_t world_idx, mpenv_world_state *out);
 /* Number of kernel launches issued by one step / one init (for bench accounting). */
 int mpenv_launches_per_step(mpenv_handle *h, uint32_t *step_launches, uint32_t *init_launches);
+/* Which ray kernels the map's BVH size selected at create():
+ *   los_pool_warps     warps per CTA of the warp-pooled visibility kernel, 0 = the per-thread kernel;
+ *   lidar_packet_ctas  CTAs per SM of the ray-packet lidar kernel (2 or 1), 0 = the per-thread kernel. */
+int mpenv_kernel_variants(mpenv_handle *h, int32_t *los_pool_warps, int32_t *lidar_packet_ctas);
 
 /* Ray census of the INSTRUMENTED build (libmpenv_b200_count.so = same sources with
  * -DMPENV_COUNT_RAYS): cumulative counts since the last reset of

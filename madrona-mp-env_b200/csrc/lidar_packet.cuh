@@ -92,7 +92,9 @@ __device__ __forceinline__ float tracePacket(const char *smem, const FastBVH &bv
     return t_max;
 }
 
-__global__ void __launch_bounds__(kPacketWarpsPerCTA * 32, MPENV_PACKET_MINB) k_lidar_packet(const __grid_constant__ KernelArgs ka)
+// <16 warps, 2 CTAs per SM> while two copies of the BVH fit in an SM's shared memory, else <32 warps, 1>.
+template <int kWarps, int kMinB>
+__global__ void __launch_bounds__(kWarps * 32, kMinB) k_lidar_packet(const __grid_constant__ KernelArgs ka)
 {
     extern __shared__ uint4 smem_raw[];
     const Ctx &c = ka.ctx;
@@ -184,12 +186,12 @@ __global__ void __launch_bounds__(kPacketWarpsPerCTA * 32, MPENV_PACKET_MINB) k_
         }
         __syncwarp();
     }
-    warpTasksDone(ka.workCounters, gridDim.x * kPacketWarpsPerCTA);
+    warpTasksDone(ka.workCounters, gridDim.x * kWarps);
 }
 
-inline size_t lidarPacketSmemBytes(uint32_t num_nodes, uint32_t num_tris)
+inline size_t lidarPacketSmemBytes(uint32_t num_nodes, uint32_t num_tris, int warps)
 {
-    return fastBVHBytes(num_nodes, num_tris) + kPacketWarpsPerCTA * sizeof(LidarPacketPool);
+    return fastBVHBytes(num_nodes, num_tris) + (size_t)warps * sizeof(LidarPacketPool);
 }
 
 }  // namespace mpenv

@@ -58,11 +58,12 @@ struct mpenv_handle {
     uint32_t snapCount = 0;
     bool snapRead[2] = { false, false };         // a D2H from this buffer has been enqueued (evRead valid)
     bool copyInFlight = false;
-    bool packetLidar = false;                // packet traversal (lidar_packet.cuh)
+    int packetLidar = 0;                     // packet traversal (lidar_packet.cuh): CTAs per SM (2, 1), 0 = per-thread k_lidar
     size_t lidarPacketSmem = 0;
     int gridLidarPacket = 0;
     bool poolLos = false;
     size_t losPoolSmem = 0;
+    int losWarps = 0;                        // warps per k_los_pool CTA (what fits beside the BVH)
     int gridLosPool = 0;
     // launch geometry
     int gridMove = 0, gridFire = 0, gridWorld = 0, gridLos = 0, gridObs = 0, gridTeam = 0, gridLidar = 0,
@@ -146,14 +147,16 @@ int gridFor(mpenv_handle *h, K kernel, int block, size_t smem, long long items)
 
 void launchLidar(mpenv_handle *h, cudaStream_t s)
 {
-    if (h->packetLidar)
-        k_lidar_packet<<<h->gridLidarPacket, kPacketWarpsPerCTA * 32, h->lidarPacketSmem, s>>>(h->ka);
+    if (h->packetLidar == 2)
+        k_lidar_packet<kPacketWarpsPerCTA, MPENV_PACKET_MINB><<<h->gridLidarPacket, kPacketWarpsPerCTA * 32, h->lidarPacketSmem, s>>>(h->ka);
+    else if (h->packetLidar == 1)
+        k_lidar_packet<32, 1><<<h->gridLidarPacket, 1024, h->lidarPacketSmem, s>>>(h->ka);
     else k_lidar<<<h->gridLidar, 160, h->bvhSmemBytes, s>>>(h->ka);
 }
 
 void launchLos(mpenv_handle *h, cudaStream_t s)
 {
-    if (h->poolLos) k_los_pool<10, 8><<<h->gridLosPool, kLosWarpsPerCTA * 32, h->losPoolSmem, s>>>(h->ka);
+    if (h->poolLos) k_los_pool<10, 8><<<h->gridLosPool, h->losWarps * 32, h->losPoolSmem, s>>>(h->ka);
     else k_los<<<h->gridLos, 128, h->bvhSmemBytes, s>>>(h->ka);
 }
 
@@ -573,21 +576,32 @@ int mpenv_create(const mpenv_config *cfg, mpenv_handle **out)
     // that path so that the tests can cover it on simple_map.
     const char *kmode = getenv("MPENV_KERNELS");
     const bool legacy = kmode && strcmp(kmode, "legacy") == 0;
-    h->losPoolSmem = losPoolSmemBytes(ka.ctx.bvh.numNodes, ka.ctx.bvh.numTris);
-    h->poolLos = !legacy && h->losPoolSmem <= 200 * 1024;
+    // one CTA per SM: as many warps as have room for their pool beside the BVH (24 on simple_map)
+    constexpr size_t kSmemPerCTA = 226 * 1024, kSmemHalfSM = 113 * 1024;
+    h->losWarps = losPoolWarps(ka.ctx.bvh.numNodes, ka.ctx.bvh.numTris, kSmemPerCTA);
+    h->poolLos = !legacy && h->losWarps >= 8;
     if (h->poolLos) {
+        h->losPoolSmem = losPoolSmemBytes(ka.ctx.bvh.numNodes, ka.ctx.bvh.numTris, h->losWarps);
         MP_CREATE(cudaFuncSetAttribute(k_los_pool<10, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->losPoolSmem));
-        h->gridLosPool = gridFor(h, k_los_pool<10, 8>, kLosWarpsPerCTA * 32, h->losPoolSmem, W * 32);
+        h->gridLosPool = gridFor(h, k_los_pool<10, 8>, h->losWarps * 32, h->losPoolSmem, W * 32);
     }
     {
-        // two CTAs per SM: each may use half of the 227 KB; the shared stack holds <= 3 pending
-        // children per tree level
-        h->lidarPacketSmem = lidarPacketSmemBytes(ka.ctx.bvh.numNodes, ka.ctx.bvh.numTris);
-        h->packetLidar = !legacy && h->lidarPacketSmem <= 110 * 1024 &&
-                         3 * bvhDepth(h->assets.nodes) + 1 <= kPacketStack;
-        if (h->packetLidar) {
-            MP_CREATE(cudaFuncSetAttribute(k_lidar_packet, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->lidarPacketSmem));
-            h->gridLidarPacket = gridFor(h, k_lidar_packet, kPacketWarpsPerCTA * 32, h->lidarPacketSmem, (N / 2) * 32);
+        // two 16-warp CTAs per SM while two copies of the BVH fit, else one 32-warp CTA; the shared
+        // stack holds <= 3 pending children per tree level
+        const size_t two = lidarPacketSmemBytes(ka.ctx.bvh.numNodes, ka.ctx.bvh.numTris, kPacketWarpsPerCTA);
+        const size_t one = lidarPacketSmemBytes(ka.ctx.bvh.numNodes, ka.ctx.bvh.numTris, 32);
+        if (!legacy && 3 * bvhDepth(h->assets.nodes) + 1 <= kPacketStack)
+            h->packetLidar = two <= kSmemHalfSM ? 2 : one <= kSmemPerCTA ? 1 : 0;
+        if (h->packetLidar == 2) {
+            h->lidarPacketSmem = two;
+            auto k = k_lidar_packet<kPacketWarpsPerCTA, MPENV_PACKET_MINB>;
+            MP_CREATE(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)two));
+            h->gridLidarPacket = gridFor(h, k, kPacketWarpsPerCTA * 32, two, (N / 2) * 32);
+        } else if (h->packetLidar == 1) {
+            h->lidarPacketSmem = one;
+            auto k = k_lidar_packet<32, 1>;
+            MP_CREATE(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)one));
+            h->gridLidarPacket = gridFor(h, k, 1024, one, (N / 2) * 32);
         }
     }
     // Sim::Sim for every world (sim.cpp:5850-5980)
@@ -1050,6 +1064,14 @@ int mpenv_launches_per_step(mpenv_handle *h, uint32_t *step_launches, uint32_t *
     if (!h) return MPENV_ERR_INVALID;
     if (step_launches) *step_launches = h->stepLaunches;
     if (init_launches) *init_launches = h->initLaunches;
+    return MPENV_OK;
+}
+
+int mpenv_kernel_variants(mpenv_handle *h, int32_t *los_pool_warps, int32_t *lidar_packet_ctas)
+{
+    if (!h) return MPENV_ERR_INVALID;
+    if (los_pool_warps) *los_pool_warps = h->poolLos ? h->losWarps : 0;
+    if (lidar_packet_ctas) *lidar_packet_ctas = h->packetLidar;
     return MPENV_OK;
 }
 

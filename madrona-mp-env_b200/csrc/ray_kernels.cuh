@@ -205,12 +205,20 @@ __global__ void __launch_bounds__(kLosWarpsPerCTA * 32, MPENV_LOS_MINB) k_los_po
         }
         __syncwarp();
     }
-    warpTasksDone(ka.workCounters + 2, gridDim.x * kLosWarpsPerCTA);
+    warpTasksDone(ka.workCounters + 2, gridDim.x * (blockDim.x >> 5));
 }
 
-inline size_t losPoolSmemBytes(uint32_t num_nodes, uint32_t num_tris)
+// The CTA is launched with as many warps (<= kLosWarpsPerCTA) as have room for their pool beside the BVH.
+inline size_t losPoolSmemBytes(uint32_t num_nodes, uint32_t num_tris, int warps)
 {
-    return fastBVHBytes(num_nodes, num_tris) + kLosWarpsPerCTA * sizeof(LosWarpPool);
+    return fastBVHBytes(num_nodes, num_tris) + (size_t)warps * sizeof(LosWarpPool);
+}
+inline int losPoolWarps(uint32_t num_nodes, uint32_t num_tris, size_t smem_limit)
+{
+    const size_t bvh = fastBVHBytes(num_nodes, num_tris);
+    if (bvh >= smem_limit) return 0;
+    const size_t w = (smem_limit - bvh) / sizeof(LosWarpPool);
+    return (int)(w < (size_t)kLosWarpsPerCTA ? w : (size_t)kLosWarpsPerCTA);
 }
 
 }  // namespace mpenv

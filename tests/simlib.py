@@ -181,20 +181,63 @@ def build_oracle():
 
 
 # ---------------------------------------------------------------------- map
-def make_scene(dst_dir, zones):
+def make_scene(dst_dir, zones=None, extra_boxes=None):
     """A copy of data/simple_map with its own zones.bin (map_importer.cpp:545-561: u32 n, AABB[n],
-    f32 rotation[n]).  zones: [(xmin, ymin, zmin, xmax, ymax, zmax, rotation), ...]."""
+    f32 rotation[n]) and / or extra axis-aligned boxes appended to collisions.bin
+    (map_importer.cpp:35-124, 233) as one more mesh each -- an affine copy of one of the map's own
+    wall boxes, so vertex order and winding are the reference's.
+    zones: [(xmin, ymin, zmin, xmax, ymax, zmax, rotation), ...];  extra_boxes: [(xmin, ymin, zmin, xmax, ymax, zmax), ...]."""
     import shutil
+    import struct
     os.makedirs(dst_dir, exist_ok=True)
     for f in os.listdir(SCENE):
-        if f != "zones.bin":
-            shutil.copy(os.path.join(SCENE, f), os.path.join(dst_dir, f))
-    z = np.asarray(zones, np.float32).reshape(-1, 7)
-    with open(os.path.join(dst_dir, "zones.bin"), "wb") as fh:
-        fh.write(np.uint32(len(z)).tobytes())
-        fh.write(np.ascontiguousarray(z[:, :6]).tobytes())
-        fh.write(np.ascontiguousarray(z[:, 6]).tobytes())
+        shutil.copy(os.path.join(SCENE, f), os.path.join(dst_dir, f))
+    if zones is not None:
+        z = np.asarray(zones, np.float32).reshape(-1, 7)
+        with open(os.path.join(dst_dir, "zones.bin"), "wb") as fh:
+            fh.write(np.uint32(len(z)).tobytes())
+            fh.write(np.ascontiguousarray(z[:, :6]).tobytes())
+            fh.write(np.ascontiguousarray(z[:, 6]).tobytes())
+    if extra_boxes:
+        b = open(os.path.join(SCENE, "collisions.bin"), "rb").read()
+        off = 24
+        nmat, nname = struct.unpack("<QQ", b[off:off + 16]); off += 16
+        head_end = off + nname + 4 * nmat
+        off = head_end
+        nmesh, nvert, ntri = struct.unpack("<QQQ", b[off:off + 24]); off += 24
+        verts = np.frombuffer(b[off:off + 12 * nvert], np.float32).reshape(-1, 3); off += 12 * nvert
+        idx = np.frombuffer(b[off:off + 12 * ntri], np.uint32).reshape(-1, 3); off += 12 * ntri
+        mats = np.frombuffer(b[off:off + 4 * ntri], np.uint32); off += 4 * ntri
+        meshes = np.frombuffer(b[off:off + 16 * nmesh], np.uint32).reshape(-1, 4)
+        tv0, tnv, tt0, tnt = [int(x) for x in meshes[5]]              # template: an interior wall box
+        tv = verts[tv0:tv0 + tnv]
+        lo, hi = tv.min(axis=0), tv.max(axis=0)
+        new_v, new_i, new_m, new_meshes = [verts], [idx], [mats], [meshes]
+        nv, nt = int(nvert), int(ntri)
+        for bx in extra_boxes:
+            blo, bhi = np.asarray(bx[:3], np.float32), np.asarray(bx[3:], np.float32)
+            new_v.append((blo + (tv - lo) / (hi - lo) * (bhi - blo)).astype(np.float32))
+            new_i.append(idx[tt0:tt0 + tnt])                             # mesh-local indices
+            new_m.append(mats[tt0:tt0 + tnt])
+            new_meshes.append(np.array([[nv, tnv, nt, tnt]], np.uint32))
+            nv += tnv; nt += tnt
+        with open(os.path.join(dst_dir, "collisions.bin"), "wb") as fh:
+            fh.write(b[:head_end])
+            fh.write(struct.pack("<QQQ", nmesh + len(extra_boxes), nv, nt))
+            for arr in (np.concatenate(new_v), np.concatenate(new_i), np.concatenate(new_m), np.concatenate(new_meshes)):
+                fh.write(np.ascontiguousarray(arr).tobytes())
     return dst_dir
+
+
+def pillar_boxes(n, seed=5):
+    """n pillars (30 x 30 x 260, standing on the floor) scattered over the open parts of simple_map,
+    away from the spawn rows at |y| ~ 1750."""
+    rng = np.random.default_rng(seed)
+    out = []
+    while len(out) < n:
+        x, y = rng.uniform(-1800, 1800), rng.uniform(-1500, 1500)
+        out.append((x, y, 0.4, x + 30.0, y + 30.0, 260.0))
+    return out
 
 
 # simple_map's three zones plus a fourth around the eastern platform, rotated 0.3 rad: the map
@@ -838,6 +881,14 @@ class GpuSim(_SimBase):
     def launches(self):
         a, b = C.c_uint32(), C.c_uint32()
         self.lib.mpenv_launches_per_step(self.h, C.byref(a), C.byref(b))
+        return a.value, b.value
+
+    def kernel_variants(self):
+        """(warps per CTA of the pooled visibility kernel, CTAs per SM of the packet lidar kernel);
+        0 = the per-thread kernel (mpenv_kernel_variants)."""
+        a, b = C.c_int32(), C.c_int32()
+        self.lib.mpenv_kernel_variants.argtypes = [C.c_void_p, C.POINTER(C.c_int32), C.POINTER(C.c_int32)]
+        self._check(self.lib.mpenv_kernel_variants(self.h, C.byref(a), C.byref(b)), "kernel_variants")
         return a.value, b.value
 
     def damaged_guards(self):

@@ -364,6 +364,31 @@ def test_large_map_fallback_kernels(monkeypatch):
         gpu.close(); orc.close()
 
 
+@pytest.mark.parametrize("pillars,los_warps,lidar_ctas", [(40, 24, 2), (110, 12, 1), (200, 0, 0), (400, 0, 0)])
+def test_larger_maps(tmp_path, pillars, los_warps, lidar_ctas):
+    """simple_map plus N pillars (12 triangles each): the kernels mpenv_create picks as the BVH outgrows
+    shared memory -- two packet-lidar CTAs per SM and a 24-warp visibility CTA (732 triangles), one
+    32-warp packet CTA and 12 visibility warps (1572), the per-thread kernels on the reference-format
+    BVH in shared memory (2652) and in L2 (5052) -- each against the oracle on the same map."""
+    scene = S.make_scene(str(tmp_path / "pillars"), extra_boxes=S.pillar_boxes(pillars))
+    W = 8
+    gpu = S.GpuSim(W, auto_reset=True, scene=scene)
+    orc = S.Oracle(W, auto_reset=True, det=True, num_threads=0, scene=scene)
+    try:
+        assert gpu.kernel_variants() == (los_warps, lidar_ctas)
+        gpu.init(); orc.init()
+        assert_same(gpu, orc, W, "init")
+        for s in range(100):
+            d, a = S.seek_policy(orc, s, W)
+            for sim in (gpu, orc):
+                sim.set_actions(d, a); sim.step()
+            if s % 10 == 9:
+                assert_same(gpu, orc, W, f"{pillars} pillars, step {s}")
+        assert gpu.damaged_guards() == 0
+    finally:
+        gpu.close(); orc.close()
+
+
 @pytest.mark.parametrize("variant,flags", [("north", 0), ("south", 128), ("sky", 8)])
 def test_zone_capture_defend_gpu(tmp_path, variant, flags):
     """Task::ZoneCaptureDefend (SURVEY 8f-4) on the synthetic 4-zone map: defender win at 8 points,

@@ -50,6 +50,26 @@ def rollout(W, steps, policy, flags=0, auto_reset=False, check_every=1, seed=10)
         host.close(); orc.close()
 
 
+def test_larger_map(built, tmp_path):
+    """simple_map plus 400 pillars (5052 triangles, a 1015-node BVH): asset reading, the BVH builder and
+    the stage functions on a map that is not the reference's own -- against the oracle on that map."""
+    scene = S.make_scene(str(tmp_path / "pillars"), extra_boxes=S.pillar_boxes(400))
+    W = 4
+    host = S.HostSim(W, auto_reset=True, scene=scene)
+    orc = S.Oracle(W, auto_reset=True, det=True, num_threads=0, scene=scene)
+    try:
+        host.init(); orc.init()
+        assert_same(host, orc, W, "init")
+        for s in range(120):
+            d, a = S.seek_policy(orc, s, W)
+            for sim in (host, orc):
+                sim.set_actions(d, a); sim.step()
+            if s % 20 == 19:
+                assert_same(host, orc, W, f"step {s}")
+    finally:
+        host.close(); orc.close()
+
+
 def random_policy(sim, s, W):
     return S.random_actions(s, W)
 
