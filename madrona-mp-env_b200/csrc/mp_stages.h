@@ -137,7 +137,9 @@ MP_HD Vec3 rotate2D(Vec3 dir, float radians)
 // applyVelocitySystem (sim.cpp:889-1028): swept-sphere character controller
 // against the static mesh only (utils.cpp:75-128 has the agent capsules
 // compiled out).
-MP_HD void applyVelocitySystem(const BVHView &bvh, Vec3 pos, Vec3 vel, int32_t cur_pose,
+// BVH: BVHView (reference format) or SphereBVH (sphere_fast.cuh) -- bvhSphereCast is overloaded.
+template <typename BVH>
+MP_HD void applyVelocitySystem(const BVH &bvh, Vec3 pos, Vec3 vel, int32_t cur_pose,
                                MoveState &move)
 {
     Vec3 x = pos;
@@ -243,7 +245,8 @@ MP_HD void applyVelocitySystem(const BVHView &bvh, Vec3 pos, Vec3 vel, int32_t c
 }
 
 // fallSystem (sim.cpp:1041-1095): constant fall rate, one downward cast.
-MP_HD void fallSystem(const BVHView &bvh, Vec3 pos, MoveState &move, float alive)
+template <typename BVH>
+MP_HD void fallSystem(const BVH &bvh, Vec3 pos, MoveState &move, float alive)
 {
     if (alive == 0.f) { move.newPos = pos; return; }
     const float FALL_RATE = 386.08858267717f;
@@ -266,7 +269,8 @@ namespace mpenv {
 // Per-agent fusion of Step-graph nodes 3-8 (sim.cpp:5403-5460): movement,
 // both aim systems, applyVelocity, updateMoveState, fall, post-fall update.
 // No cross-agent reads.
-MP_HD void stageMove(const Ctx &c, int idx)
+template <typename BVH>
+MP_HD void stageMove(const Ctx &c, const BVH &bvh, int idx)
 {
     const SimPtrs &p = c.p;
     float alive = p.alive[idx];
@@ -281,10 +285,10 @@ MP_HD void stageMove(const Ctx &c, int idx)
     stageBot(c, idx);            // policy id -1: plan + apply the scripted bot's action rows
     movementSystem(p.actDiscrete[idx], rot, vel, alive, combat, stand, move);
     aimSystems(p.actAim[idx], p.actDiscreteAim[idx], rot, aim, alive);
-    applyVelocitySystem(c.bvh, pos, vel, stand.cur, move);
+    applyVelocitySystem(bvh, pos, vel, stand.cur, move);
     pos = move.newPos;          // updateMoveStateSystem (sim.cpp:1030-1039)
     vel = move.newVel;
-    fallSystem(c.bvh, pos, move, alive);
+    fallSystem(bvh, pos, move, alive);
     pos = move.newPos;          // updateMoveStatePostFallSystem (sim.cpp:1097-1104)
 
     p.pos[idx] = pos;
@@ -295,6 +299,8 @@ MP_HD void stageMove(const Ctx &c, int idx)
     p.move[idx] = move;
     p.combat[idx].remainingRespawnSteps = combat.remainingRespawnSteps;
 }
+
+MP_HD void stageMove(const Ctx &c, int idx) { stageMove(c, c.bvh, idx); }
 
 }  // namespace mpenv
 

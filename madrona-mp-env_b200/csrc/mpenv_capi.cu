@@ -63,6 +63,8 @@ struct mpenv_handle {
     int gridLidarPacket = 0;
     bool poolLos = false;
     size_t losPoolSmem = 0;
+    bool fastMove = false;                   // k_move<true>: SphereNodes in shared memory (sphere_fast.cuh)
+    size_t moveSmem = 0;
     int losWarps = 0;                        // warps per k_los_pool CTA (what fits beside the BVH)
     int gridLosPool = 0;
     // launch geometry
@@ -145,6 +147,12 @@ int gridFor(mpenv_handle *h, K kernel, int block, size_t smem, long long items)
     return (int)(want < cap ? want : cap);
 }
 
+void launchMove(mpenv_handle *h, cudaStream_t s)
+{
+    if (h->fastMove) k_move<true><<<h->gridMove, 128, h->moveSmem, s>>>(h->ka);
+    else k_move<false><<<h->gridMove, 128, h->bvhSmemBytes, s>>>(h->ka);
+}
+
 void launchLidar(mpenv_handle *h, cudaStream_t s)
 {
     if (h->packetLidar == 2)
@@ -178,7 +186,7 @@ uint32_t launchStep(mpenv_handle *h, cudaStream_t s)
 {
     uint32_t n = 0;
     if (!h->replayLog) {
-        k_move<<<h->gridMove, 128, h->bvhSmemBytes, s>>>(h->ka); n++;
+        launchMove(h, s); n++;
         if (h->cold) k_fire<true><<<h->gridFire, 128, h->bvhSmemBytes, s>>>(h->ka);
         else k_fire<false><<<h->gridFire, 128, h->bvhSmemBytes, s>>>(h->ka);
         n++;
@@ -553,7 +561,7 @@ int mpenv_create(const mpenv_config *cfg, mpenv_handle **out)
     MP_CREATE(cudaMemcpyAsync(ka.ctx.p.trainCtrl, &tc, sizeof(tc), cudaMemcpyHostToDevice, h->stream));
 
     if (h->bvhSmemBytes > 48 * 1024) {
-        MP_CREATE(cudaFuncSetAttribute(k_move, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->bvhSmemBytes));
+        MP_CREATE(cudaFuncSetAttribute(k_move<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->bvhSmemBytes));
         MP_CREATE(cudaFuncSetAttribute(k_fire<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->bvhSmemBytes));
         MP_CREATE(cudaFuncSetAttribute(k_fire<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->bvhSmemBytes));
         MP_CREATE(cudaFuncSetAttribute(k_los, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->bvhSmemBytes));
@@ -561,7 +569,7 @@ int mpenv_create(const mpenv_config *cfg, mpenv_handle **out)
     }
 
     const long long W = cfg->num_worlds, N = W * kAgents;
-    h->gridMove = gridFor(h, k_move, 128, h->bvhSmemBytes, N);
+    h->gridMove = gridFor(h, k_move<false>, 128, h->bvhSmemBytes, N);
     h->gridFire = h->cold ? gridFor(h, k_fire<true>, 128, h->bvhSmemBytes, N) : gridFor(h, k_fire<false>, 128, h->bvhSmemBytes, N);
     h->gridWorld = h->cold ? gridFor(h, k_world<true>, 128, 0, W * 16) : gridFor(h, k_world<false>, 128, 0, W * 16);
     h->gridLos = gridFor(h, k_los, 128, h->bvhSmemBytes, N * kTeamSize);
@@ -576,6 +584,13 @@ int mpenv_create(const mpenv_config *cfg, mpenv_handle **out)
     // that path so that the tests can cover it on simple_map.
     const char *kmode = getenv("MPENV_KERNELS");
     const bool legacy = kmode && strcmp(kmode, "legacy") == 0;
+    // sphere casts on radius-expanded float bounds (sphere_fast.cuh) while five CTAs' copies fit in an SM
+    h->moveSmem = sphereBVHBytes(ka.ctx.bvh.numNodes, ka.bvhVertWords);
+    h->fastMove = !legacy && h->moveSmem <= 44 * 1024;
+    if (h->fastMove) {
+        MP_CREATE(cudaFuncSetAttribute(k_move<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->moveSmem));
+        h->gridMove = gridFor(h, k_move<true>, 128, h->moveSmem, N);
+    }
     // one CTA per SM: as many warps as have room for their pool beside the BVH (24 on simple_map)
     constexpr size_t kSmemPerCTA = 226 * 1024, kSmemHalfSM = 113 * 1024;
     h->losWarps = losPoolWarps(ka.ctx.bvh.numNodes, ka.ctx.bvh.numTris, kSmemPerCTA);
@@ -1019,7 +1034,7 @@ int mpenv_step_timed(mpenv_handle *h, float *kernel_ms, const char **kernel_name
     for (int i = 0; i < 9; i++) MP_CUDA(h, cudaEventCreate(&ev[i]));
     uint32_t n = 0;
     MP_CUDA(h, cudaEventRecord(ev[0], s));
-    k_move<<<h->gridMove, 128, h->bvhSmemBytes, s>>>(h->ka); names[n++] = "k_move"; cudaEventRecord(ev[n], s);
+    launchMove(h, s); names[n++] = "k_move"; cudaEventRecord(ev[n], s);
     k_fire<false><<<h->gridFire, 128, h->bvhSmemBytes, s>>>(h->ka); names[n++] = "k_fire"; cudaEventRecord(ev[n], s);
     k_world<false><<<h->gridWorld, 128, 0, s>>>(h->ka); names[n++] = "k_world"; cudaEventRecord(ev[n], s);
     launchLos(h, s); names[n++] = "k_los"; cudaEventRecord(ev[n], s);

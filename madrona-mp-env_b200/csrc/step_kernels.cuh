@@ -21,6 +21,7 @@
 #include <cuda_runtime.h>
 
 #include "mp_stages.h"
+#include "sphere_fast.cuh"
 #include "world_coop.cuh"
 
 namespace mpenv {
@@ -106,20 +107,33 @@ __global__ void __launch_bounds__(128) k_reset(KernelArgs ka)
 #ifndef MPENV_MOVE_MINB
 #define MPENV_MOVE_MINB 5       // 96 registers, 20 warps / SM: 0.161 -> 0.149 ms despite 208 B of spills
 #endif
+// kFast: the sphere casts run on SphereNodes staged in shared memory (sphere_fast.cuh); else on the
+// reference-format BVH (shared memory or, for a map that does not fit, L2).
+template <bool kFast>
 __global__ void __launch_bounds__(128, MPENV_MOVE_MINB) k_move(KernelArgs ka)
 {
     extern __shared__ uint4 smem_raw[];
     Ctx c = ka.ctx;
-    c.bvh = stageBVH(ka, reinterpret_cast<uint32_t *>(smem_raw));
     const int N = (int)c.cfg.numWorlds * kAgents;
     // 1 .. 11 sphere casts per agent: 32-agent chunks are drawn dynamically (a static stride
     // gave 1.3 agents per thread, i.e. a second, 30 %-full round)
     const int chunks = (N + 31) / 32;
-    for (;;) {
-        const int chunk = fetchWarpTask(ka.workCounters + 4);
-        if (chunk >= chunks) break;
-        const int i = chunk * 32 + (int)(threadIdx.x & 31);
-        if (i < N) stageMove(c, i);
+    if (kFast) {
+        const SphereBVH sb = stageSphereBVH(c.bvh, ka.bvhVertWords, kAgentRadius, smem_raw);
+        for (;;) {
+            const int chunk = fetchWarpTask(ka.workCounters + 4);
+            if (chunk >= chunks) break;
+            const int i = chunk * 32 + (int)(threadIdx.x & 31);
+            if (i < N) stageMove(c, sb, i);
+        }
+    } else {
+        c.bvh = stageBVH(ka, reinterpret_cast<uint32_t *>(smem_raw));
+        for (;;) {
+            const int chunk = fetchWarpTask(ka.workCounters + 4);
+            if (chunk >= chunks) break;
+            const int i = chunk * 32 + (int)(threadIdx.x & 31);
+            if (i < N) stageMove(c, i);
+        }
     }
     warpTasksDone(ka.workCounters + 4, gridDim.x * (blockDim.x >> 5));
 }
