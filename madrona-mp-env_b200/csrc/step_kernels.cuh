@@ -105,7 +105,7 @@ __global__ void __launch_bounds__(128) k_reset(KernelArgs ka)
 }
 
 #ifndef MPENV_MOVE_MINB
-#define MPENV_MOVE_MINB 5       // 96 registers, 20 warps / SM: 0.161 -> 0.149 ms despite 208 B of spills
+#define MPENV_MOVE_MINB 6       // 80 registers, 24 warps / SM (measured 5: 0.101 ms, 6: 0.096, 7: 0.102)
 #endif
 // kFast: the sphere casts run on SphereNodes staged in shared memory (sphere_fast.cuh); else on the
 // reference-format BVH (shared memory or, for a map that does not fit, L2).
