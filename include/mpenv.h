@@ -217,6 +217,19 @@ int mpenv_episode_stats_async(mpenv_handle *h, void *cuda_stream, int64_t **dev_
 /* Synchronous host variant: reduces on the handle's stream and copies the
  * MPENV_NUM_STATS values to `host_out`. */
 int mpenv_episode_stats(mpenv_handle *h, int64_t *host_out);
+/* The same reduction for callers that must not allocate (code under CUDA graph capture, serving
+ * loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+ * Writes MPENV_NUM_STATS int64 values to `dev_out`, a DEVICE buffer the
+ * caller owns, stream-ordered on `cuda_stream`; the call allocates nothing (no cudaMalloc / cudaFree /
+ * allocating library routine).  Its scratch -- per-CTA partial sums and a ticket, 33 KB -- is a static
+ * device array that every GPU loading the library holds until exit, so:
+ *   - a handle with more than MPENV_STATIC_STATS_MAX_WORLDS worlds is rejected (MPENV_ERR_INVALID,
+ *     mpenv_last_error() names the limit);
+ *   - all calls on one GPU share the scratch: calls that overlap on the GPU (two streams, two handles,
+ *     two processes do NOT share it) race; order them on one stream or with events.
+ * The values are identical to mpenv_episode_stats_async's (integer sums). */
+#define MPENV_STATIC_STATS_MAX_WORLDS 65536u
+int mpenv_episode_stats_static(mpenv_handle *h, void *cuda_stream, int64_t *dev_out);
 
 /* ---- logs ---------------------------------------------------
  * Event log: GameEvent (24 B: u32 type, u32 pad, u64 matchID, u32 step, 4 payload

@@ -4,6 +4,7 @@
 // (src/mgr.cpp:305-662, 1213-1912) for the per-step simulation path.
 #include <cstdio>
 #include <cstring>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -90,6 +91,73 @@ struct mpenv_handle {
 };
 
 constexpr size_t kGuardBytes = 256;
+
+// ---- episode statistics without any allocation (mpenv_episode_stats_static) ------------------
+// k_stats accumulates into a cudaMalloc'ed buffer with atomics.  This variant keeps its scratch --
+// one row of partial sums per CTA plus a ticket -- in a file-scope device array that every GPU
+// loading the library holds until exit (kStaticStatsBytes = 33 KB), and writes the totals to the
+// CALLER's buffer: each CTA stores its partials, the last CTA to take a ticket adds the rows up in
+// CTA order.  In host code `g_static_stats` is only a stand-in for the symbol: the device address
+// comes from cudaGetSymbolAddress, once per device (staticStatsScratch below).
+constexpr int kStaticStatsMaxCTAs = 256;
+constexpr int kStaticStatsRow = MPENV_NUM_STATS;                       // u64 per CTA
+constexpr size_t kStaticStatsWords = (size_t)kStaticStatsMaxCTAs * kStaticStatsRow + 32;   // + the ticket's own 256 B
+constexpr size_t kStaticStatsBytes = kStaticStatsWords * sizeof(unsigned long long);
+static __device__ __align__(256) unsigned long long g_static_stats[kStaticStatsWords];
+
+namespace mpenv {
+__global__ void __launch_bounds__(256) k_stats_static(KernelArgs ka, unsigned long long *scratch, unsigned long long *out)
+{
+    __shared__ long long warp_sums[8][13];
+    __shared__ bool last_cta;
+    const Ctx &c = ka.ctx;
+    const int W = (int)c.cfg.numWorlds;
+    unsigned long long *ticket = scratch + (size_t)kStaticStatsMaxCTAs * kStaticStatsRow;
+    long long acc[13];
+    for (int k = 0; k < 13; k++) acc[k] = 0;
+    for (int w = blockIdx.x * blockDim.x + threadIdx.x; w < W; w += gridDim.x * blockDim.x) {
+        acc[0] += 1;
+        const MatchResult &mr = c.p.matchResult[w];
+        if (c.p.done[w * kAgents]) {
+            acc[1] += 1;
+            if (mr.winResult >= 0 && mr.winResult <= 2) acc[2 + mr.winResult] += 1;
+            acc[5] += mr.teamTotalKills[0]; acc[6] += mr.teamTotalKills[1];
+            acc[7] += mr.teamObjectivePoints[0]; acc[8] += mr.teamObjectivePoints[1];
+        }
+        for (int a = 0; a < kAgents; a++) {
+            const int idx = w * kAgents + a;
+            acc[9] += c.p.alive[idx] != 0.f ? 1 : 0;
+            acc[10] += c.p.done[idx];
+            acc[11] += (long long)llrintf(c.p.reward[idx] * 1.0e6f);
+        }
+        acc[12] += c.p.world[w].match.curStep;
+    }
+    for (int k = 0; k < 13; k++) {
+        long long v = acc[k];
+        for (int off = 16; off > 0; off >>= 1) v += __shfl_down_sync(0xFFFFFFFFu, v, off);
+        if ((threadIdx.x & 31) == 0) warp_sums[threadIdx.x >> 5][k] = v;
+    }
+    __syncthreads();
+    if (threadIdx.x < kStaticStatsRow) {
+        long long v = 0;
+        if (threadIdx.x < 13)
+            for (int wp = 0; wp < 8; wp++) v += warp_sums[wp][threadIdx.x];
+        scratch[(size_t)blockIdx.x * kStaticStatsRow + threadIdx.x] = (unsigned long long)v;   // every word of the row
+        __threadfence();
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) last_cta = atomicAdd(ticket, 1ull) == (unsigned long long)gridDim.x - 1ull;
+    __syncthreads();
+    if (!last_cta) return;
+    __threadfence();
+    if (threadIdx.x < kStaticStatsRow) {
+        unsigned long long v = 0;
+        for (unsigned b = 0; b < gridDim.x; b++) v += __ldcg(scratch + (size_t)b * kStaticStatsRow + threadIdx.x);
+        out[threadIdx.x] = v;
+    }
+    if (threadIdx.x == 0) *ticket = 0;
+}
+}  // namespace mpenv
 
 namespace {
 
@@ -331,6 +399,30 @@ int copyInterface(mpenv_handle *h, cudaStream_t s, void **buffers, bool inputs)
         if (inputs) MP_CUDA(h, cudaMemcpyAsync(d.dev_ptr, buffers[i], tensorBytes(d), cudaMemcpyDeviceToDevice, s));
         else MP_CUDA(h, cudaMemcpyAsync(buffers[i], d.dev_ptr, tensorBytes(d), cudaMemcpyDeviceToDevice, s));
     }
+    return MPENV_OK;
+}
+
+}  // namespace
+
+namespace {
+
+// Device address of g_static_stats on `device` (which must be current): resolved once per device.
+constexpr int kStaticStatsMaxDevices = 64;
+unsigned long long *g_static_stats_ptr[kStaticStatsMaxDevices] = {};
+std::mutex g_static_stats_mutex;
+
+int staticStatsScratch(mpenv_handle *h, unsigned long long **out)
+{
+    if (h->device < 0 || h->device >= kStaticStatsMaxDevices)
+        return fail(h, MPENV_ERR_INVALID, "mpenv_episode_stats_static: device ordinal beyond 63");
+    std::lock_guard<std::mutex> lock(g_static_stats_mutex);
+    if (!g_static_stats_ptr[h->device]) {
+        unsigned long long *ptr = nullptr;
+        MP_CUDA(h, cudaGetSymbolAddress((void **)&ptr, g_static_stats));
+        if (!ptr) return fail(h, MPENV_ERR_CUDA, "mpenv_episode_stats_static: cudaGetSymbolAddress returned a null address");
+        g_static_stats_ptr[h->device] = ptr;
+    }
+    *out = g_static_stats_ptr[h->device];
     return MPENV_OK;
 }
 
@@ -994,6 +1086,31 @@ int mpenv_episode_stats(mpenv_handle *h, int64_t *host_out)
     if (rc != MPENV_OK) return rc;
     MP_CUDA(h, cudaMemcpyAsync(host_out, dev, sizeof(int64_t) * MPENV_NUM_STATS, cudaMemcpyDeviceToHost, h->stream));
     MP_CUDA(h, cudaStreamSynchronize(h->stream));
+    return MPENV_OK;
+}
+
+int mpenv_episode_stats_static(mpenv_handle *h, void *cuda_stream, int64_t *dev_out)
+{
+    if (!h || !dev_out) return MPENV_ERR_INVALID;
+    if (h->cfg.num_worlds > MPENV_STATIC_STATS_MAX_WORLDS) {
+        char buf[160];
+        snprintf(buf, sizeof(buf), "mpenv_episode_stats_static: %u worlds exceed the static scratch's maximum of %u "
+                 "(use mpenv_episode_stats_async)", (unsigned)h->cfg.num_worlds, (unsigned)MPENV_STATIC_STATS_MAX_WORLDS);
+        return fail(h, MPENV_ERR_INVALID, buf);
+    }
+    MP_CUDA(h, cudaSetDevice(h->device));
+    unsigned long long *scratch = nullptr;
+    const int rc = staticStatsScratch(h, &scratch);
+    if (rc != MPENV_OK) return rc;
+    cudaStream_t s = (cudaStream_t)cuda_stream;
+    int grid = (int)((h->cfg.num_worlds + 255) / 256);
+    if (grid > kStaticStatsMaxCTAs) grid = kStaticStatsMaxCTAs;
+    if (grid < 1) grid = 1;
+    // the ticket must start at zero whatever an earlier (possibly aborted) call left; the partial rows
+    // are overwritten in full by the CTAs that the last one reads
+    MP_CUDA(h, cudaMemsetAsync(scratch + (size_t)kStaticStatsMaxCTAs * kStaticStatsRow, 0, sizeof(unsigned long long), s));
+    k_stats_static<<<grid, 256, 0, s>>>(h->ka, scratch, reinterpret_cast<unsigned long long *>(dev_out));
+    MP_CUDA(h, cudaGetLastError());
     return MPENV_OK;
 }
 
