@@ -98,7 +98,7 @@ __global__ void __launch_bounds__(kWarps * 32, kMinB) k_lidar_packet(const __gri
 {
     extern __shared__ uint4 smem_raw[];
     const Ctx &c = ka.ctx;
-    const FastBVH bvh = stageFastBVH(c.bvh, smem_raw);
+    const FastBVH bvh = stageFastBVH(ka.fastImage, c.bvh.numNodes, c.bvh.numTris, smem_raw);
     const size_t bvh_bytes = fastBVHBytes(c.bvh.numNodes, c.bvh.numTris);
     const char *smem = reinterpret_cast<const char *>(smem_raw);
     LidarPacketPool &P = reinterpret_cast<LidarPacketPool *>(reinterpret_cast<char *>(smem_raw) + bvh_bytes)[threadIdx.x >> 5];

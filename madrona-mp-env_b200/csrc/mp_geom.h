@@ -227,14 +227,22 @@ MP_HD float rayZCapsule(Vec3 o, Vec3 d, float r, float h)
     return t_hit == FLT_MAX ? 0.f : t_hit;
 }
 
+// The static-mesh part of traceRayAgainstWorld as a functor, so that a kernel can substitute
+// its own traversal of the same BVH (ray_fast.cuh) without touching the logic around it.
+struct RefMeshTrace {
+    const BVHView &bvh;
+    MP_HD bool operator()(Vec3 o, Vec3 d, float *t) const { return bvhTraceRay(bvh, o, d, t); }
+};
+
 // reference utils.cpp:10-72.  agent_pos: the world's 12 agent positions.
 // Returns hit flag; *hit_agent = agent index or -1 for the static mesh.
-MP_HD bool traceRayWorld(const BVHView &bvh, const Vec3 *agent_pos, Vec3 o, Vec3 d,
-                         float *hit_t_out, int32_t *hit_agent_out)
+template <class MeshTrace>
+MP_HD bool traceRayWorldWith(const MeshTrace &mesh, const Vec3 *agent_pos, Vec3 o, Vec3 d,
+                             float *hit_t_out, int32_t *hit_agent_out)
 {
     float min_hit_t = FLT_MAX;
     float t;
-    bool hit = bvhTraceRay(bvh, o, d, &t);
+    bool hit = mesh(o, d, &t);
     if (hit) min_hit_t = t;
     int32_t hit_agent = -1;
     for (int i = 0; i < kAgents; i++) {
@@ -252,6 +260,12 @@ MP_HD bool traceRayWorld(const BVHView &bvh, const Vec3 *agent_pos, Vec3 o, Vec3
     *hit_t_out = min_hit_t;
     *hit_agent_out = hit_agent;
     return hit;
+}
+
+MP_HD bool traceRayWorld(const BVHView &bvh, const Vec3 *agent_pos, Vec3 o, Vec3 d,
+                         float *hit_t_out, int32_t *hit_agent_out)
+{
+    return traceRayWorldWith(RefMeshTrace{bvh}, agent_pos, o, d, hit_t_out, hit_agent_out);
 }
 
 // -------------------------------------------------------------- sphere cast

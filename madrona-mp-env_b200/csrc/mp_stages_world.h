@@ -45,8 +45,9 @@ MP_HD void logAgentEvent(const Ctx &c, int w, int a, int slot, uint32_t type, ui
 // fireSystem (sim.cpp:1443-1615).  Reads the world's 12 post-move positions
 // and the target's HP / respawn timer; writes only this agent's rows plus
 // DamageDealt[target][own team offset] (conflict-free: one slot per shooter).
-template <bool kCold = true>
-MP_HD void stageFire(const Ctx &c, int w, int a, const Vec3 *world_pos)
+// mesh: the static-mesh ray cast (RefMeshTrace, or a kernel's own traversal of the same BVH).
+template <bool kCold, class MeshTrace>
+MP_HD void stageFire(const Ctx &c, int w, int a, const Vec3 *world_pos, const MeshTrace &mesh)
 {
     const SimPtrs &p = c.p;
     const int idx = w * kAgents + a;
@@ -105,7 +106,7 @@ MP_HD void stageFire(const Ctx &c, int w, int a, const Vec3 *world_pos)
     float hit_t;
     int32_t hit_agent;
     MP_COUNT_RAYS(2, 1);
-    bool hit = traceRayWorld(c.bvh, world_pos, fire_from, fire_dir, &hit_t, &hit_agent);
+    bool hit = traceRayWorldWith(mesh, world_pos, fire_from, fire_dir, &hit_t, &hit_agent);
     cs.firedShotT = hit ? hit_t : FLT_MAX;
 
     bool hit_success = hit;
@@ -126,6 +127,12 @@ MP_HD void stageFire(const Ctx &c, int w, int a, const Vec3 *world_pos)
         p.dmg[(size_t)(w * kAgents + hit_agent) * kTeamSize + offsetOf(a)] = ws.dmgPerBullet;
     }
     p.combat[idx] = cs;
+}
+
+template <bool kCold = true>
+MP_HD void stageFire(const Ctx &c, int w, int a, const Vec3 *world_pos)
+{
+    stageFire<kCold>(c, w, a, world_pos, RefMeshTrace{c.bvh});
 }
 
 // ============================================================ world stages

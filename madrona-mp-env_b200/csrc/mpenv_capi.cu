@@ -64,6 +64,8 @@ struct mpenv_handle {
     int gridLidarPacket = 0;
     bool poolLos = false;
     size_t losPoolSmem = 0;
+    bool fastFire = false;                   // k_fire_fast: the shot on the FastBVH in shared memory (ray_kernels.cuh)
+    size_t fireSmem = 0;
     bool fastMove = false;                   // k_move<true>: SphereNodes in shared memory (sphere_fast.cuh)
     size_t moveSmem = 0;
     int losWarps = 0;                        // warps per k_los_pool CTA (what fits beside the BVH)
@@ -221,6 +223,17 @@ void launchMove(mpenv_handle *h, cudaStream_t s)
     else k_move<false><<<h->gridMove, 128, h->bvhSmemBytes, s>>>(h->ka);
 }
 
+void launchFire(mpenv_handle *h, cudaStream_t s)
+{
+    if (h->fastFire) {
+        if (h->cold) k_fire_fast<true><<<h->gridFire, 128, h->fireSmem, s>>>(h->ka);
+        else k_fire_fast<false><<<h->gridFire, 128, h->fireSmem, s>>>(h->ka);
+    } else {
+        if (h->cold) k_fire<true><<<h->gridFire, 128, h->bvhSmemBytes, s>>>(h->ka);
+        else k_fire<false><<<h->gridFire, 128, h->bvhSmemBytes, s>>>(h->ka);
+    }
+}
+
 void launchLidar(mpenv_handle *h, cudaStream_t s)
 {
     if (h->packetLidar == 2)
@@ -255,8 +268,7 @@ uint32_t launchStep(mpenv_handle *h, cudaStream_t s)
     uint32_t n = 0;
     if (!h->replayLog) {
         launchMove(h, s); n++;
-        if (h->cold) k_fire<true><<<h->gridFire, 128, h->bvhSmemBytes, s>>>(h->ka);
-        else k_fire<false><<<h->gridFire, 128, h->bvhSmemBytes, s>>>(h->ka);
+        launchFire(h, s);
         n++;
     } else if (h->eventLog) {
         // pvpReplayLogic has no fireSystem: no fire events this step
@@ -683,6 +695,14 @@ int mpenv_create(const mpenv_config *cfg, mpenv_handle **out)
         MP_CREATE(cudaFuncSetAttribute(k_move<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->moveSmem));
         h->gridMove = gridFor(h, k_move<true>, 128, h->moveSmem, N);
     }
+    // hitscan on the re-encoded BVH while five CTAs' copies fit in an SM
+    h->fireSmem = fastBVHBytes(ka.ctx.bvh.numNodes, ka.ctx.bvh.numTris);
+    h->fastFire = !legacy && h->fireSmem <= 44 * 1024;
+    if (h->fastFire) {
+        MP_CREATE(cudaFuncSetAttribute(k_fire_fast<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->fireSmem));
+        MP_CREATE(cudaFuncSetAttribute(k_fire_fast<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->fireSmem));
+        h->gridFire = h->cold ? gridFor(h, k_fire_fast<true>, 128, h->fireSmem, N) : gridFor(h, k_fire_fast<false>, 128, h->fireSmem, N);
+    }
     // one CTA per SM: as many warps as have room for their pool beside the BVH (24 on simple_map)
     constexpr size_t kSmemPerCTA = 226 * 1024, kSmemHalfSM = 113 * 1024;
     h->losWarps = losPoolWarps(ka.ctx.bvh.numNodes, ka.ctx.bvh.numTris, kSmemPerCTA);
@@ -710,6 +730,23 @@ int mpenv_create(const mpenv_config *cfg, mpenv_handle **out)
             MP_CREATE(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)one));
             h->gridLidarPacket = gridFor(h, k, 1024, one, (N / 2) * 32);
         }
+    }
+    // The re-encoded BVH images are built once here; the kernels stage them with plain 16-byte copies.
+    ka.fastImage = nullptr;
+    ka.sphereImage = nullptr;
+    if (h->fastFire || h->poolLos || h->packetLidar) {
+        void *img = nullptr;
+        if (!devAlloc(&img, fastBVHBytes(ka.ctx.bvh.numNodes, ka.ctx.bvh.numTris))) return bail(MPENV_ERR_CUDA);
+        k_encode_fast_bvh<<<1, 256, 0, h->stream>>>(ka.ctx.bvh, img);
+        MP_CREATE(cudaGetLastError());
+        ka.fastImage = reinterpret_cast<const uint4 *>(img);
+    }
+    if (h->fastMove) {
+        void *img = nullptr;
+        if (!devAlloc(&img, h->moveSmem)) return bail(MPENV_ERR_CUDA);
+        k_encode_sphere_bvh<<<1, 256, 0, h->stream>>>(ka.ctx.bvh, ka.bvhVertWords, kAgentRadius, img);
+        MP_CREATE(cudaGetLastError());
+        ka.sphereImage = reinterpret_cast<const uint4 *>(img);
     }
     // Sim::Sim for every world (sim.cpp:5850-5980)
     k_ctor<<<h->gridSmall, 128, 0, h->stream>>>(ka);
@@ -1152,7 +1189,7 @@ int mpenv_step_timed(mpenv_handle *h, float *kernel_ms, const char **kernel_name
     uint32_t n = 0;
     MP_CUDA(h, cudaEventRecord(ev[0], s));
     launchMove(h, s); names[n++] = "k_move"; cudaEventRecord(ev[n], s);
-    k_fire<false><<<h->gridFire, 128, h->bvhSmemBytes, s>>>(h->ka); names[n++] = "k_fire"; cudaEventRecord(ev[n], s);
+    launchFire(h, s); names[n++] = "k_fire"; cudaEventRecord(ev[n], s);
     k_world<false><<<h->gridWorld, 128, 0, s>>>(h->ka); names[n++] = "k_world"; cudaEventRecord(ev[n], s);
     launchLos(h, s); names[n++] = "k_los"; cudaEventRecord(ev[n], s);
     k_obs<<<h->gridObs, 128, 0, s>>>(h->ka); names[n++] = "k_obs"; cudaEventRecord(ev[n], s);

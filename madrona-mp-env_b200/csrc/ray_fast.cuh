@@ -65,10 +65,12 @@ __host__ __device__ inline size_t fastBVHBytes(uint32_t num_nodes, uint32_t num_
     return (size_t)num_nodes * sizeof(FastNode) + (size_t)(num_tris + 1) * sizeof(FastTri);
 }
 
-// Re-encodes the reference-format BVH (global memory) into `smem`.
-__device__ __forceinline__ FastBVH stageFastBVH(const BVHView &g, void *smem)
+// Re-encodes the reference-format BVH into the FastBVH image at `dst` (FastNode[numNodes], then
+// FastTri[numTris + 1]); the threads of ONE CTA.  Done once per simulator (k_encode_fast_bvh); the
+// kernels copy the image into their shared memory.
+__device__ __forceinline__ void encodeFastBVH(const BVHView &g, void *dst)
 {
-    FastNode *sn = reinterpret_cast<FastNode *>(smem);
+    FastNode *sn = reinterpret_cast<FastNode *>(dst);
     FastTri *st = reinterpret_cast<FastTri *>(sn + g.numNodes);
     for (uint32_t i = threadIdx.x; i < g.numNodes * 4u; i += blockDim.x) {
         const uint32_t n = i >> 2, k = i & 3u;
@@ -105,10 +107,20 @@ __device__ __forceinline__ FastBVH stageFastBVH(const BVHView &g, void *smem)
         const uint32_t t = i / 12u, k = i - t * 12u;
         st[t].v[k] = k < 9u ? gv[t * 9u + k] : 0.f;
     }
+}
+
+__global__ void __launch_bounds__(256) k_encode_fast_bvh(BVHView g, void *dst) { encodeFastBVH(g, dst); }
+
+// Copies the FastBVH image (global memory, 16-byte units) into `smem`.
+__device__ __forceinline__ FastBVH stageFastBVH(const uint4 *image, uint32_t num_nodes, uint32_t num_tris, void *smem)
+{
+    const uint32_t n16 = (uint32_t)(fastBVHBytes(num_nodes, num_tris) / 16);
+    uint4 *d = reinterpret_cast<uint4 *>(smem);
+    for (uint32_t i = threadIdx.x; i < n16; i += blockDim.x) d[i] = __ldg(image + i);
     __syncthreads();
     FastBVH f;
-    f.nodes = sn;
-    f.tris = st;
+    f.nodes = reinterpret_cast<const FastNode *>(smem);
+    f.tris = reinterpret_cast<const FastTri *>(f.nodes + num_nodes);
     return f;
 }
 
@@ -504,6 +516,61 @@ __device__ __forceinline__ void traversePool(const char *smem, const FastBVH &bv
         }
     }
 }
+
+// One ray, one thread: the reference traversal (mesh_bvh.inl:110-208) on the FastBVH, for the few
+// rays that do not come in pools or packets (the hitscan of fireSystem: 0.08 per agent-step).
+// Same visiting order as bvhTraceRay -- children in slot order, leaves inline, internal children
+// pushed and popped LIFO -- at a quarter of its instructions per node visit.
+struct FastMeshTrace {
+    const char *smem;            // the CTA's dynamic shared memory, which starts with the FastBVH
+    FastBVH bvh;
+    float one;
+    __device__ bool operator()(Vec3 o, Vec3 d, float *t_out) const
+    {
+        const RayDirRec rec = makeRayDirRec(d);
+        RayRegs r;
+        setRay(r, o.x, o.y, o.z, rec.invX, rec.invY, rec.invZ, 0);
+        TriConsts tc;
+        tc.Sx = rec.tri.Sx; tc.Sy = rec.tri.Sy; tc.Sz = rec.tri.Sz;
+        tc.kx = rec.tri.kperm & 3; tc.ky = (rec.tri.kperm >> 2) & 3; tc.kz = (rec.tri.kperm >> 4) & 3;
+        tc.okx = sel3(tc.kx, o.x, o.y, o.z);
+        tc.oky = sel3(tc.ky, o.x, o.y, o.z);
+        tc.okz = sel3(tc.kz, o.x, o.y, o.z);
+        int32_t stack[32];
+        int32_t sp = 0;
+        stack[sp++] = 0;
+        float t_max = FLT_MAX;
+        while (sp > 0) {
+            const char *nd = smem + (uint32_t)stack[--sp] * (uint32_t)sizeof(FastNode);
+            float tn[4];
+            if (r.offX >= 0) {
+                visitNode(nd, r, one, tn);
+            } else {
+                const float4 v = visitNodeRef(nd, r.ox, r.oy, r.oz, r.invX, r.invY, r.invZ);
+                tn[0] = v.x; tn[1] = v.y; tn[2] = v.z; tn[3] = v.w;
+            }
+            const uint32_t meta = reinterpret_cast<const uint32_t *>(nd)[3];
+            const int4 ch = reinterpret_cast<const int4 *>(nd)[2];
+            const int32_t child[4] = { ch.x, ch.y, ch.z, ch.w };
+#pragma unroll
+            for (int i = 0; i < 4; i++) {
+                if (!(tn[i] <= t_max)) continue;
+                if ((meta >> i) & 1u) {
+                    const FastTri *tri = bvh.tris + (child[i] & 0x7FFFFFFF);
+                    const int ntri = (int)((meta >> (4 + 7 * i)) & 0x7Fu);
+                    for (int k = 0; k < ntri; k++) {
+                        float t;
+                        if (rayTriangleFast(tri + k, tc, t_max, &t)) t_max = t;
+                    }
+                } else {
+                    stack[sp++] = child[i];
+                }
+            }
+        }
+        *t_out = t_max;
+        return t_max != FLT_MAX;
+    }
+};
 
 // ---- agent capsules (utils.cpp:39-61 + rayZCapsule of mp_geom.h) -------------
 // Everything of the capsule test that depends on (ray origin, agent) only.

@@ -17,6 +17,24 @@ namespace mpenv {
 constexpr int kLidarRaysPerAgent = kFwdLidarH * kFwdLidarW + kRearLidarH * kRearLidarW;   // 80
 constexpr int kLidarTaskRays = 2 * kLidarRaysPerAgent;                                    // 160
 
+// ----------------------------------------------------------------- hitscan
+// k_fire (step_kernels.cuh) with the shot traced on the FastBVH (FastMeshTrace).
+template <bool kCold>
+__global__ void __launch_bounds__(128) k_fire_fast(KernelArgs ka)
+{
+    extern __shared__ uint4 smem_raw[];
+    const Ctx &c = ka.ctx;
+    FastMeshTrace mesh;
+    mesh.bvh = stageFastBVH(ka.fastImage, c.bvh.numNodes, c.bvh.numTris, smem_raw);
+    mesh.smem = reinterpret_cast<const char *>(smem_raw);
+    mesh.one = ka.one;
+    const int N = (int)c.cfg.numWorlds * kAgents;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < N; i += gridDim.x * blockDim.x) {
+        const int w = i / kAgents, a = i - w * kAgents;
+        stageFire<kCold>(c, w, a, c.p.pos + (size_t)w * kAgents, mesh);
+    }
+}
+
 // --------------------------------------------------------------------- LOS
 // opponentsWriteVisibilitySystem (sim.cpp:2526-2560) + isAgentVisible
 // (utils.cpp:186-271).  One warp owns a world: 12 agents x 6 opponents x 4 sample
@@ -74,7 +92,7 @@ __global__ void __launch_bounds__(kLosWarpsPerCTA * 32, MPENV_LOS_MINB) k_los_po
 {
     extern __shared__ uint4 smem_raw[];
     const Ctx &c = ka.ctx;
-    const FastBVH bvh = stageFastBVH(c.bvh, smem_raw);
+    const FastBVH bvh = stageFastBVH(ka.fastImage, c.bvh.numNodes, c.bvh.numTris, smem_raw);
     const size_t bvh_bytes = fastBVHBytes(c.bvh.numNodes, c.bvh.numTris);
     LosWarpPool *pools = reinterpret_cast<LosWarpPool *>(reinterpret_cast<char *>(smem_raw) + bvh_bytes);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;

@@ -38,15 +38,17 @@ struct SphereBVH {
     const Vec3 *verts;         // 3 per triangle, de-indexed, leaf order (+ one pad triangle)
 };
 
-inline size_t sphereBVHBytes(uint32_t num_nodes, uint32_t vert_words)
+__host__ __device__ inline size_t sphereBVHBytes(uint32_t num_nodes, uint32_t vert_words)
 {
     return (size_t)num_nodes * sizeof(SphereNode) + (((size_t)vert_words * 4 + 15) / 16) * 16;
 }
 
-// Re-encodes the reference-format BVH (global memory) into `smem` for casts of radius `sphere_r`.
-__device__ __forceinline__ SphereBVH stageSphereBVH(const BVHView &g, uint32_t vert_words, float sphere_r, void *smem)
+// Re-encodes the reference-format BVH into the image at `dst` (SphereNode[numNodes], then the vertices)
+// for casts of radius `sphere_r`; the threads of ONE CTA.  Done once per simulator
+// (k_encode_sphere_bvh); k_move copies the image into its shared memory.
+__device__ __forceinline__ void encodeSphereBVH(const BVHView &g, uint32_t vert_words, float sphere_r, void *dst)
 {
-    SphereNode *sn = reinterpret_cast<SphereNode *>(smem);
+    SphereNode *sn = reinterpret_cast<SphereNode *>(dst);
     uint32_t *sv = reinterpret_cast<uint32_t *>(sn + g.numNodes);
     for (uint32_t i = threadIdx.x; i < g.numNodes * 4u; i += blockDim.x) {
         const uint32_t n = i >> 2, k = i & 3u;
@@ -70,10 +72,26 @@ __device__ __forceinline__ SphereBVH stageSphereBVH(const BVHView &g, uint32_t v
     }
     const uint32_t *gv = reinterpret_cast<const uint32_t *>(g.verts);
     for (uint32_t i = threadIdx.x; i < vert_words; i += blockDim.x) sv[i] = __ldg(gv + i);
+    // the image is copied in 16-byte units: define the tail
+    const uint32_t padded = (uint32_t)((((size_t)vert_words * 4 + 15) / 16) * 4);
+    for (uint32_t i = vert_words + threadIdx.x; i < padded; i += blockDim.x) sv[i] = 0;
+}
+
+__global__ void __launch_bounds__(256) k_encode_sphere_bvh(BVHView g, uint32_t vert_words, float sphere_r, void *dst)
+{
+    encodeSphereBVH(g, vert_words, sphere_r, dst);
+}
+
+// Copies the SphereBVH image (global memory, 16-byte units) into `smem`.
+__device__ __forceinline__ SphereBVH stageSphereBVH(const uint4 *image, uint32_t num_nodes, uint32_t vert_words, void *smem)
+{
+    const uint32_t n16 = (uint32_t)(((size_t)num_nodes * sizeof(SphereNode) + (((size_t)vert_words * 4 + 15) / 16) * 16) / 16);
+    uint4 *d = reinterpret_cast<uint4 *>(smem);
+    for (uint32_t i = threadIdx.x; i < n16; i += blockDim.x) d[i] = __ldg(image + i);
     __syncthreads();
     SphereBVH f;
-    f.nodes = sn;
-    f.verts = reinterpret_cast<const Vec3 *>(sv);
+    f.nodes = reinterpret_cast<const SphereNode *>(smem);
+    f.verts = reinterpret_cast<const Vec3 *>(f.nodes + num_nodes);
     return f;
 }
 

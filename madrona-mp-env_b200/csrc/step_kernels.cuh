@@ -32,6 +32,8 @@ struct KernelArgs {
     uint32_t bvhVertWords;   // 32-bit words of vertex data (incl. the pad triangle)
     int32_t bvhInSmem;       // 1: stage into shared memory, 0: traverse from global / L2
     uint32_t *workCounters;  // device-wide task counters of the dynamically scheduled kernels (zero between launches)
+    const uint4 *fastImage;  // FastBVH image (ray_fast.cuh), null when no kernel uses it
+    const uint4 *sphereImage;// SphereBVH image (sphere_fast.cuh), null when k_move runs on the reference format
     float one;               // 1.0f, opaque to ptxas: keeps the two roundings of q * dq + oq apart (ray_fast.cuh)
 };
 
@@ -119,7 +121,7 @@ __global__ void __launch_bounds__(128, MPENV_MOVE_MINB) k_move(KernelArgs ka)
     // gave 1.3 agents per thread, i.e. a second, 30 %-full round)
     const int chunks = (N + 31) / 32;
     if (kFast) {
-        const SphereBVH sb = stageSphereBVH(c.bvh, ka.bvhVertWords, kAgentRadius, smem_raw);
+        const SphereBVH sb = stageSphereBVH(ka.sphereImage, c.bvh.numNodes, ka.bvhVertWords, smem_raw);
         for (;;) {
             const int chunk = fetchWarpTask(ka.workCounters + 4);
             if (chunk >= chunks) break;
