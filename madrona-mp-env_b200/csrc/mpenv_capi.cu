@@ -710,7 +710,7 @@ int mpenv_create(const mpenv_config *cfg, mpenv_handle **out)
     if (h->poolLos) {
         h->losPoolSmem = losPoolSmemBytes(ka.ctx.bvh.numNodes, ka.ctx.bvh.numTris, h->losWarps);
         MP_CREATE(cudaFuncSetAttribute(k_los_pool<10, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->losPoolSmem));
-        h->gridLosPool = gridFor(h, k_los_pool<10, 8>, h->losWarps * 32, h->losPoolSmem, W * 32);
+        h->gridLosPool = gridFor(h, k_los_pool<10, 8>, h->losWarps * 32, h->losPoolSmem, W * 2 * 32);
     }
     {
         // two 16-warp CTAs per SM while two copies of the BVH fit, else one 32-warp CTA; the shared

@@ -37,8 +37,9 @@ __global__ void __launch_bounds__(128) k_fire_fast(KernelArgs ka)
 
 // --------------------------------------------------------------------- LOS
 // opponentsWriteVisibilitySystem (sim.cpp:2526-2560) + isAgentVisible
-// (utils.cpp:186-271).  One warp owns a world: 12 agents x 6 opponents x 4 sample
-// points = 288 candidates.  Most die in the alive / view-space cull; survivors
+// (utils.cpp:186-271).  One warp owns one TEAM of a world as observers: 6 agents x 6
+// opponents x 4 sample points = 144 candidates (a world per task left each warp with
+// 2.3 tasks at 8192 worlds: the hand-out's tail was a third of a task long).  Most die in the alive / view-space cull; survivors
 // are compacted into the warp's ray pool (ballot rank), traversed with dynamic
 // refill.  A sample sees its target iff the closest hit of traceRayAgainstWorld
 // IS the target; that is decided exactly without finishing every traversal:
@@ -51,7 +52,7 @@ __global__ void __launch_bounds__(128) k_fire_fast(KernelArgs ka)
 #endif
 constexpr int kLosWarpsPerCTA = MPENV_LOS_WARPS;
 constexpr int kLosPoolCap = 96;
-constexpr int kLosCandidates = kAgents * kTeamSize * 4;      // 288
+constexpr int kLosCandidates = kTeamSize * kTeamSize * 4;    // 144
 
 struct __align__(16) LosWarpPool {
     RayDirRec dirs[kLosPoolCap];
@@ -62,7 +63,7 @@ struct __align__(16) LosWarpPool {
     float tmesh[kLosPoolCap];
     float tstop[kLosPoolCap];        // distance to the target capsule: a mesh hit at t <= tstop blocks
     int32_t meta[kLosPoolCap];       // observer | target << 4 | pair << 8
-    uint32_t seen[4];                // bit per (observer, opponent slot) pair: 72 bits
+    uint32_t seen[4];                // bit per (observer, opponent slot) pair of the task's team: 36 bits
     int32_t alive;                   // bit per agent
     int32_t pad[3];
 };
@@ -100,11 +101,12 @@ __global__ void __launch_bounds__(kLosWarpsPerCTA * 32, MPENV_LOS_MINB) k_los_po
     LosWarpPool &P = pools[warp];
     const SimPtrs &p = c.p;
     const float *fr = c.mc->frustum;
-    const int W = (int)c.cfg.numWorlds;
+    const int num_tasks = (int)c.cfg.numWorlds * 2;
 
     for (;;) {
-        const int w = fetchWarpTask(ka.workCounters + 2);
-        if (w >= W) break;
+        const int task = fetchWarpTask(ka.workCounters + 2);
+        if (task >= num_tasks) break;
+        const int w = task >> 1, team = task & 1;
         const int base = w * kAgents;
         // ---- per-agent terms (utils.cpp:240-251)
         if (lane < 4) P.seen[lane] = 0;
@@ -133,9 +135,10 @@ __global__ void __launch_bounds__(kLosWarpsPerCTA * 32, MPENV_LOS_MINB) k_los_po
                 const int32_t cd = cand + lane;
                 cand += 32;
                 const int32_t pair = cd >> 2, s = cd & 3;
-                const int32_t a = pair / kTeamSize, j = pair - a * kTeamSize;
-                const int32_t opp = (teamOf(a) ^ 1) * kTeamSize + j;
-                bool ok = ((alive_m >> a) & 1u) && ((alive_m >> opp) & 1u);
+                const int32_t a_off = pair / kTeamSize, j = pair - a_off * kTeamSize;
+                const int32_t a = team * kTeamSize + a_off;
+                const int32_t opp = (team ^ 1) * kTeamSize + j;
+                bool ok = cd < kLosCandidates && ((alive_m >> a) & 1u) && ((alive_m >> opp) & 1u);   // 144 = 4.5 warps
                 Vec3 dir = v3(0.f, 1.f, 0.f);
                 if (ok) {
                     const float4 o4 = P.origin[a], t4 = P.target[opp], q4 = P.invRot[a], r4 = P.dRight[a];
@@ -207,9 +210,9 @@ __global__ void __launch_bounds__(kLosWarpsPerCTA * 32, MPENV_LOS_MINB) k_los_po
             }
             __syncwarp();
         }
-        // ---- export: canSee[agent][8] bytes, 12 agents x 8 B contiguous per world
-        if (lane < kAgents * 2) {
-            const int32_t a = lane >> 1, half = lane & 1;
+        // ---- export: canSee[agent][8] bytes, the team's 6 agents x 8 B contiguous
+        if (lane < kTeamSize * 2) {
+            const int32_t a = lane >> 1, half = lane & 1;     // a: offset within the team, as in `pair`
             uint32_t word = 0;
 #pragma unroll
             for (int k = 0; k < 4; k++) {
@@ -219,7 +222,7 @@ __global__ void __launch_bounds__(kLosWarpsPerCTA * 32, MPENV_LOS_MINB) k_los_po
                     if ((P.seen[pair >> 5] >> (pair & 31)) & 1u) word |= 1u << (8 * k);
                 }
             }
-            reinterpret_cast<uint32_t *>(p.canSee)[(size_t)base * 2 + lane] = word;
+            reinterpret_cast<uint32_t *>(p.canSee)[(size_t)(base + team * kTeamSize) * 2 + lane] = word;
         }
         __syncwarp();
     }
