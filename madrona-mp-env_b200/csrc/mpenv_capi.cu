@@ -50,6 +50,8 @@ struct mpenv_handle {
     bool fullTeam = false;
     // pipelined host read-back (mpenv_read_tensors_pipelined)
     cudaStream_t copyStream = nullptr;
+    cudaStream_t lidarStream = nullptr;      // captured into the graphs as the lidar branch (launchObsPhase)
+    cudaEvent_t evFork = nullptr, evJoin = nullptr;
     cudaEvent_t evSnap[2] = { nullptr, nullptr }, evRead[2] = { nullptr, nullptr }, evCopied = nullptr;
     char *snapshot[2] = { nullptr, nullptr };    // double-buffered: snapshot t+1 is taken while t goes to the host
     size_t snapshotBytes = 0;
@@ -253,9 +255,24 @@ void launchLos(mpenv_handle *h, cudaStream_t s)
 // sim.cpp:5174-5320): visibility -> masks + observations -> full-team -> lidar.
 uint32_t launchObsPhase(mpenv_handle *h, cudaStream_t s)
 {
-    // One stream: lidar beside visibility -> observations on a forked graph branch was
-    // measured slower (3.17 vs 3.02 ms/step; the persistent lidar grid already fills every SM).
     uint32_t n = 0;
+    if (h->lidarStream) {
+        // Lidar needs nothing from visibility / observations (it reads what k_world left), so the
+        // graph forks: {visibility -> observation rows} beside {lidar}.  The visibility CTAs and the
+        // lidar CTAs each fill an SM, so those two still run one after the other, but the hand-out
+        // tail of visibility and the whole latency-bound observation kernel (24 % issue) now run
+        // under lidar's ramp-up instead of in front of it: 1.233 -> 1.207 ms per step.
+        cudaEventRecord(h->evFork, s);
+        cudaStreamWaitEvent(h->lidarStream, h->evFork, 0);
+        launchLos(h, s); n++;
+        launchLidar(h, h->lidarStream); n++;
+        k_obs<<<h->gridObs, 128, 0, s>>>(h->ka); n++;
+        cudaEventRecord(h->evJoin, h->lidarStream);
+        cudaStreamWaitEvent(s, h->evJoin, 0);
+        return n;
+    }
+    // with the full-team tensors: k_fullteam gathers the PREVIOUS step's lidar rows (the reference's
+    // task order, sim.cpp:5174-5320), so lidar stays behind it
     launchLos(h, s); n++;
     k_obs<<<h->gridObs, 128, 0, s>>>(h->ka); n++;
     if (h->fullTeam) { k_fullteam<<<h->gridTeam, 128, 0, s>>>(h->ka); n++; }
@@ -462,6 +479,9 @@ void mpenv_destroy(mpenv_handle *h)
         if (h->snapshot[k]) cudaFree(h->snapshot[k]);
     }
     if (h->evCopied) cudaEventDestroy(h->evCopied);
+    if (h->evFork) cudaEventDestroy(h->evFork);
+    if (h->evJoin) cudaEventDestroy(h->evJoin);
+    if (h->lidarStream) cudaStreamDestroy(h->lidarStream);
     if (h->stream) cudaStreamDestroy(h->stream);
     delete h;
 }
@@ -747,6 +767,11 @@ int mpenv_create(const mpenv_config *cfg, mpenv_handle **out)
         k_encode_sphere_bvh<<<1, 256, 0, h->stream>>>(ka.ctx.bvh, ka.bvhVertWords, kAgentRadius, img);
         MP_CREATE(cudaGetLastError());
         ka.sphereImage = reinterpret_cast<const uint4 *>(img);
+    }
+    if (!h->fullTeam) {
+        MP_CREATE(cudaStreamCreateWithFlags(&h->lidarStream, cudaStreamNonBlocking));
+        MP_CREATE(cudaEventCreateWithFlags(&h->evFork, cudaEventDisableTiming));
+        MP_CREATE(cudaEventCreateWithFlags(&h->evJoin, cudaEventDisableTiming));
     }
     // Sim::Sim for every world (sim.cpp:5850-5980)
     k_ctor<<<h->gridSmall, 128, 0, h->stream>>>(ka);

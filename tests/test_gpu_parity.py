@@ -339,6 +339,8 @@ def test_lidar_packets_vs_oracle(W):
             for name in ("fwd_lidar", "rear_lidar"):
                 assert np.array_equal(gpu.export(name).view(np.int32), orc.export(name).view(np.int32)), \
                     f"step {step}: {name}"
+            if step % 10 == 9:       # the forked graph (no full-team tensors): every output, not only lidar
+                assert_same(gpu, orc, W, f"step {step}", full_team=False)
     finally:
         gpu.close(); orc.close()
 
@@ -372,18 +374,21 @@ def test_larger_maps(tmp_path, pillars, los_warps, lidar_ctas):
     BVH in shared memory (2652) and in L2 (5052) -- each against the oracle on the same map."""
     scene = S.make_scene(str(tmp_path / "pillars"), extra_boxes=S.pillar_boxes(pillars))
     W = 8
-    gpu = S.GpuSim(W, auto_reset=True, scene=scene)
+    # without the full-team tensors the graphs fork (lidar beside visibility -> observations, mpenv_capi.cu):
+    # covered on one packet and one per-thread kernel selection
+    full_team = pillars in (40, 200)
+    gpu = S.GpuSim(W, auto_reset=True, scene=scene, full_team=full_team)
     orc = S.Oracle(W, auto_reset=True, det=True, num_threads=0, scene=scene)
     try:
         assert gpu.kernel_variants() == (los_warps, lidar_ctas)
         gpu.init(); orc.init()
-        assert_same(gpu, orc, W, "init")
+        assert_same(gpu, orc, W, "init", full_team=full_team)
         for s in range(100):
             d, a = S.seek_policy(orc, s, W)
             for sim in (gpu, orc):
                 sim.set_actions(d, a); sim.step()
             if s % 10 == 9:
-                assert_same(gpu, orc, W, f"{pillars} pillars, step {s}")
+                assert_same(gpu, orc, W, f"{pillars} pillars, step {s}", full_team=full_team)
         assert gpu.damaged_guards() == 0
     finally:
         gpu.close(); orc.close()
