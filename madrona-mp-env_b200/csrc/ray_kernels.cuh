@@ -176,10 +176,19 @@ __global__ void __launch_bounds__(kLosWarpsPerCTA * 32, MPENV_LOS_MINB) k_los_po
                                               dir.x, dir.y, dir.z, a2, dd);
                     }
                     ok = t_tgt != 0.f;
-                    for (int i = 0; i < kAgents && ok; i++) {
-                        if (i == opp) continue;
+                    // the other capsules whose axis the ray passes within r + 2 of (for the rest t would be 0):
+                    // a branch-free 12-bit mask, then a loop over the few set bits
+                    uint32_t near = 0;
+#pragma unroll
+                    for (int i = 0; i < kAgents; i++) {
+                        const float2 t2 = *reinterpret_cast<const float2 *>(&P.target[i]);
+                        near |= capsuleMayHit(o4.x - t2.x, o4.y - t2.y, dir.x, dir.y, a2) ? 1u << i : 0u;
+                    }
+                    near &= ~(1u << opp);
+                    while (near && ok) {
+                        const int i = __ffs(near) - 1;
+                        near &= near - 1u;
                         const float4 t4 = P.target[i];
-                        if (!capsuleMayHit(o4.x - t4.x, o4.y - t4.y, dir.x, dir.y, a2)) continue;   // t would be 0
                         const float t = rayCapsuleRec(makeCapsuleRec(v3(o4.x, o4.y, o4.z), v3(t4.x, t4.y, t4.z)),
                                                       dir.x, dir.y, dir.z, a2, dd);
                         if (t != 0.f && (i < opp ? !(t_tgt < t) : (t < t_tgt))) ok = false;
