@@ -30,7 +30,7 @@ mult = {'Mbyte': 1e6, 'Kbyte': 1e3, 'byte': 1, 'Gbyte': 1e9}
 tr = {}
 for r in data:
     n = r[ix['Kernel Name']]
-    key = 'k_los' if 'k_los' in n else 'k_lidar' if 'k_lidar' in n else n.split('(')[0].replace('void ', '').split('<')[0]
+    key = 'k_los' if 'k_los' in n else 'k_lidar' if 'k_lidar' in n else 'k_fire' if 'k_fire' in n else n.split('(')[0].replace('void ', '').split('<')[0]
     tr[key] = int(sum(float(r[ix[m]]) * mult[units[ix[m]]] for m in ('dram__bytes_read.sum', 'dram__bytes_write.sum')))
 json.dump({"source": f"profiles/{tag}_ncu_full_summary.csv (ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum per launch, {worlds} worlds)",
            "worlds": worlds, "csrc_sha16": csrc_digest(), "bytes_per_launch": tr}, open(os.path.join(ROOT, 'profiles', 'ncu_traffic.json'), 'w'), indent=1)
