@@ -1,3 +1,4 @@
+#include <cfloat>
 // assets.cpp -- see assets.h.
 #include "assets.h"
 
@@ -372,6 +373,25 @@ bool fillMapConsts(const MapAssets &assets, MapConsts *mc, std::string *err)
         float hi = 1.f / sqrtf(hx * hx + hy * hy);
         mc->frustum[0] = wx * wi; mc->frustum[1] = wy * wi;
         mc->frustum[2] = hx * hi; mc->frustum[3] = hy * hi;
+    }
+    {   // vertex occupancy grid (mp_geom.h: sphereSweepMayTouchMirroredVertex); every vertex the casts can
+        // read, the pad triangle included
+        float lo[2] = { FLT_MAX, FLT_MAX }, hi[2] = { -FLT_MAX, -FLT_MAX };
+        for (const Vec3 &v : assets.verts) {
+            lo[0] = fminf(lo[0], v.x); hi[0] = fmaxf(hi[0], v.x);
+            lo[1] = fminf(lo[1], v.y); hi[1] = fmaxf(hi[1], v.y);
+        }
+        if (assets.verts.empty()) { lo[0] = lo[1] = 0.f; hi[0] = hi[1] = 1.f; }
+        mc->vertGridMinX = lo[0];
+        mc->vertGridMinY = lo[1];
+        mc->vertGridInvCellX = (float)kVertGrid / fmaxf(hi[0] - lo[0], 1.f);
+        mc->vertGridInvCellY = (float)kVertGrid / fmaxf(hi[1] - lo[1], 1.f);
+        for (const Vec3 &v : assets.verts) {
+            int i = (int)((v.x - lo[0]) * mc->vertGridInvCellX), j = (int)((v.y - lo[1]) * mc->vertGridInvCellY);
+            i = i < 0 ? 0 : (i >= kVertGrid ? kVertGrid - 1 : i);
+            j = j < 0 ? 0 : (j >= kVertGrid ? kVertGrid - 1 : j);
+            mc->vertGrid[(j * kVertGrid + i) >> 5] |= 1u << ((j * kVertGrid + i) & 31);
+        }
     }
     if (assets.aSpawns.size() > kMaxSpawns || assets.bSpawns.size() > kMaxSpawns ||
         assets.respawns.size() >= kMaxSpawns || assets.zoneBoxes.size() > kMaxZones) {

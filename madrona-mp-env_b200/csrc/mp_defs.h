@@ -300,6 +300,7 @@ struct NavView {
     uint32_t numTris;
 };
 
+constexpr int kVertGrid = 64;
 struct MapConsts {
     AABB worldBounds;
     float maxDist;                      // Sim::maxDist (sim.cpp:5855)
@@ -317,6 +318,10 @@ struct MapConsts {
     // (sim.cpp:3347-3350; theta depends only on the column index)
     float fwdLidarX[kFwdLidarW], fwdLidarY[kFwdLidarW];
     float rearLidarX[kRearLidarW], rearLidarY[kRearLidarW];
+    // Occupancy of the mesh vertices on a kVertGrid x kVertGrid grid over x, y (bit = some vertex in
+    // the cell): what sphereSweepMayTouchMirroredVertex (mp_geom.h) looks up.
+    float vertGridMinX, vertGridMinY, vertGridInvCellX, vertGridInvCellY;
+    uint32_t vertGrid[kVertGrid * kVertGrid / 32];
 };
 
 struct SimConfig {

@@ -355,8 +355,49 @@ MP_HD float sphereCastVert(Vec3 ray_o, Vec3 ray_d, float sphere_r2, Vec3 v, floa
 }
 
 // reference mesh_bvh.inl:885-1127.  *out_n is written only on a hit.
+// Bounded sweeps (bvhSphereCast's t_bound) and the reference's float arithmetic: the edge test of a
+// LONG edge (axis_len2 ~ 2e6 times |start|^2 ~ 2e6, differences of products near 5e12) reports contact
+// when the sphere is still up to ~0.02 units farther than its radius from the edge, i.e. BEFORE the
+// sphere reaches the triangle's plane: grazing a 1300-unit wall at 15.008 units the reference's own
+// loop returns the diagonal edge at t = 6.88 although plane_t = 7.16.  The reference's result then
+// depends on whether some EARLIER triangle of its unbounded sweep has already pulled t_max below
+// plane_t -- state a bounded sweep does not have.  So a bounded sweep also DETECTS whether such a hit
+// is possible (kSweepSlack is a generous bound on that error, in distance units) and reports it through
+// `risky`; the caller then repeats the cast unbounded, which is the reference's loop itself.
+#ifndef MPENV_SWEEP_SLACK
+#define MPENV_SWEEP_SLACK 0.5f
+#endif
+constexpr float kSweepSlack = MPENV_SWEEP_SLACK;
+
+// The three edge and three vertex tests of sphereCastTriangle, from the running bound hit_t.
+MP_HD float sphereCastFeatures(Vec3 e01, Vec3 e02, Vec3 e12, Vec3 v0, Vec3 v1, Vec3 v2, Vec3 ray_o, Vec3 ray_d,
+                               float sphere_r2, float hit_t)
+{
+    const float ray_d_len2 = length2(ray_d);
+    hit_t = sphereCastEdge(ray_d, ray_d_len2, sphere_r2, e01, v0, hit_t);
+    hit_t = sphereCastEdge(ray_d, ray_d_len2, sphere_r2, e02, v0, hit_t);
+    hit_t = sphereCastEdge(ray_d, ray_d_len2, sphere_r2, e12, v1, hit_t);
+    hit_t = sphereCastVert(ray_o, ray_d, sphere_r2, v0, hit_t);
+    hit_t = sphereCastVert(ray_o, ray_d, sphere_r2, v1, hit_t);
+    hit_t = sphereCastVert(ray_o, ray_d, sphere_r2, v2, hit_t);
+    return hit_t;
+}
+
+// Detection only: would the feature tests of this triangle report contact before t_max?
+MP_HD bool sphereCastFeaturesBefore(Vec3 tri_a, Vec3 tri_b, Vec3 tri_c, Vec3 ray_o, Vec3 ray_d, float t_max,
+                                    float sphere_r)
+{
+    const Vec3 e01 = tri_b - tri_a, e02 = tri_c - tri_a, e12 = tri_c - tri_b;
+    const Vec3 v0 = tri_a - ray_o, v1 = tri_b - ray_o, v2 = tri_c - ray_o;
+    return sphereCastFeatures(e01, e02, e12, v0, v1, v2, ray_o, ray_d, sphere_r * sphere_r, t_max) < t_max;
+}
+
+// detect (bounded sweeps): returns kSweepRisky (< 0, no contact time is) when the plane early-out below
+// hides a feature hit (see kSweepSlack).
+constexpr float kSweepRisky = -1.f;
 MP_HD_NOINLINE float sphereCastTriangle(Vec3 tri_a, Vec3 tri_b, Vec3 tri_c, Vec3 ray_o,
-                                        Vec3 ray_d, float t_max, float sphere_r, Vec3 *out_n)
+                                        Vec3 ray_d, float t_max, float sphere_r, Vec3 *out_n,
+                                        bool detect = false)
 {
     const Vec3 e01 = tri_b - tri_a, e02 = tri_c - tri_a, e12 = tri_c - tri_b;
     const Vec3 v0 = tri_a - ray_o, v1 = tri_b - ray_o, v2 = tri_c - ray_o;
@@ -382,7 +423,15 @@ MP_HD_NOINLINE float sphereCastTriangle(Vec3 tri_a, Vec3 tri_b, Vec3 tri_c, Vec3
             Vec3 extruded_delta = (sgn * sphere_r) * n;
             Vec3 v0_ext = v0 - extruded_delta;
             float plane_t = dot(v0_ext, n) / n_dot_d;
-            if (plane_t * abs_n_dot_d < -sphere_r || plane_t >= t_max) return t_max;
+            if (plane_t * abs_n_dot_d < -sphere_r) return t_max;
+            if (plane_t >= t_max) {
+                // the plane is reached at or after the bound; the features can only be (mis)reported
+                // before it if the sphere is within the slack of the plane by then
+                if (detect && (plane_t - t_max) * abs_n_dot_d <= kSweepSlack &&
+                    sphereCastFeatures(e01, e02, e12, v0, v1, v2, ray_o, ray_d, sphere_r2, t_max) < t_max)
+                    return kSweepRisky;
+                return t_max;
+            }
             if (plane_t >= 0.0f) {
                 Vec3 e = cross(ray_d, v0_ext);
                 float v = -dot(e02, e) * sgn;
@@ -395,14 +444,7 @@ MP_HD_NOINLINE float sphereCastTriangle(Vec3 tri_a, Vec3 tri_b, Vec3 tri_c, Vec3
         }
     }
 
-    const float ray_d_len2 = length2(ray_d);
-    float hit_t = t_max;
-    hit_t = sphereCastEdge(ray_d, ray_d_len2, sphere_r2, e01, v0, hit_t);
-    hit_t = sphereCastEdge(ray_d, ray_d_len2, sphere_r2, e02, v0, hit_t);
-    hit_t = sphereCastEdge(ray_d, ray_d_len2, sphere_r2, e12, v1, hit_t);
-    hit_t = sphereCastVert(ray_o, ray_d, sphere_r2, v0, hit_t);
-    hit_t = sphereCastVert(ray_o, ray_d, sphere_r2, v1, hit_t);
-    hit_t = sphereCastVert(ray_o, ray_d, sphere_r2, v2, hit_t);
+    const float hit_t = sphereCastFeatures(e01, e02, e12, v0, v1, v2, ray_o, ray_d, sphere_r2, t_max);
     if (hit_t >= t_max) return t_max;
 
     Vec3 hit_pt = ray_d * hit_t;
@@ -451,10 +493,17 @@ MP_HD bool sphereCastNodeCheck(Vec3 o, Vec3 inv_d, float t_max, float sphere_r,
 // infinity (mesh_bvh.inl:760) and the step then clamps the result to the
 // distance moved this tick; bounding the sweep skips the far side of the map.
 MP_HD_NOINLINE float bvhSphereCast(const BVHView &bvh, Vec3 ray_o, Vec3 ray_d, float sphere_r,
-                                   Vec3 *out_n, float t_bound = FLT_MAX)
+                                   Vec3 *out_n, float t_bound = FLT_MAX, bool *risky = nullptr)
 {
     MP_COUNT_RAYS(3, 1);
     Vec3 inv_d = v3(1.f / ray_d.x, 1.f / ray_d.y, 1.f / ray_d.z);
+    // risky (bounded sweeps): see kSweepSlack.  Besides the plane early-out inside sphereCastTriangle,
+    // the bound culls nodes the reference's unbounded sweep would enter later; a subtree whose boxes,
+    // grown by the slack, are entered BEFORE the bound is walked in a detect-only mode (its triangles'
+    // feature tests only).  Needed only until the first hit: from then on the running bound is the
+    // reference's own.
+    constexpr int32_t kDetectOnly = 0x40000000;
+    const bool detect = risky != nullptr && t_bound < FLT_MAX;
     int32_t stack[32];
     int32_t stack_size = 0;
     stack[stack_size++] = 0;
@@ -462,7 +511,9 @@ MP_HD_NOINLINE float bvhSphereCast(const BVHView &bvh, Vec3 ray_o, Vec3 ray_d, f
     const float t_max = t_bound;
     float hit_t = t_max;
     while (stack_size > 0) {
-        const BVHNode &node = bvh.nodes[stack[--stack_size]];
+        const int32_t entry = stack[--stack_size];
+        const bool detect_only = (entry & kDetectOnly) != 0;
+        const BVHNode &node = bvh.nodes[entry & ~kDetectOnly];
         const float sx = u2f(((uint32_t)(int32_t)node.expX + 127u) << 23);
         const float sy = u2f(((uint32_t)(int32_t)node.expY + 127u) << 23);
         const float sz = u2f(((uint32_t)(int32_t)node.expZ + 127u) << 23);
@@ -475,15 +526,33 @@ MP_HD_NOINLINE float bvhSphereCast(const BVHView &bvh, Vec3 ray_o, Vec3 ray_d, f
             Vec3 bmax = v3(node.minX + sx * (float)node.qMaxX[i],
                            node.minY + sy * (float)node.qMaxY[i],
                            node.minZ + sz * (float)node.qMaxZ[i]);
-            if (!sphereCastNodeCheck(ray_o, inv_d, hit_t, sphere_r, bmin, bmax)) continue;
+            if (detect_only || !sphereCastNodeCheck(ray_o, inv_d, hit_t, sphere_r, bmin, bmax)) {
+                if (!detect || *risky || hit_t < t_max) continue;
+                // the reference comes here only if the sweep meets the box at all; a feature inside can be
+                // (mis)reported before the bound only if the grown box is entered before the bound
+                if (!sphereCastNodeCheck(ray_o, inv_d, FLT_MAX, sphere_r, bmin, bmax)) continue;
+                if (!sphereCastNodeCheck(ray_o, inv_d, t_max, sphere_r + kSweepSlack, bmin, bmax)) continue;
+                if (child & 0x80000000) {
+                    const int32_t leaf_idx = child & ~0x80000000;
+                    for (int k = 0; k < 2; k++) {
+                        const Vec3 *tv = bvh.verts + (size_t)(leaf_idx + k) * 3;
+                        if (sphereCastFeaturesBefore(tv[0], tv[1], tv[2], ray_o, ray_d, t_max, sphere_r)) *risky = true;
+                    }
+                } else {
+                    stack[stack_size++] = child | kDetectOnly;
+                }
+                continue;
+            }
             if (child & 0x80000000) {
                 int32_t leaf_idx = child & ~0x80000000;
                 Vec3 leaf_n = v3(0.f, 0.f, 0.f);
                 float leaf_t = hit_t;
                 for (int k = 0; k < 2; k++) {
                     const Vec3 *tv = bvh.verts + (size_t)(leaf_idx + k) * 3;
-                    leaf_t = sphereCastTriangle(tv[0], tv[1], tv[2], ray_o, ray_d, leaf_t,
-                                                sphere_r, &leaf_n);
+                    const float t = sphereCastTriangle(tv[0], tv[1], tv[2], ray_o, ray_d, leaf_t,
+                                                       sphere_r, &leaf_n, detect);
+                    if (t < 0.f) *risky = true;        // kSweepRisky: leaf_t stays
+                    else leaf_t = t;
                 }
                 if (leaf_t < hit_t) { hit_t = leaf_t; closest_n = leaf_n; }
             } else {
@@ -493,6 +562,53 @@ MP_HD_NOINLINE float bvhSphereCast(const BVHView &bvh, Vec3 ray_o, Vec3 ray_d, f
     }
     if (hit_t < t_max) *out_n = closest_n;
     return hit_t < t_max ? hit_t : FLT_MAX;
+}
+
+// When is a BOUNDED sweep (t_bound above) exact?  sphereCastVert is handed the ORIGIN-RELATIVE vertex
+// and subtracts it from the absolute ray origin (see its comment: the reference's quirk, kept), so next
+// to every real vertex v a cast also tests a sphere around the MIRRORED point v - ray_o -- a point that
+// has nothing to do with where v's triangle sits in the BVH.  The argument above ("a culled node's box
+// is entered at t >= t_bound") covers a triangle's real features only: a mirrored vertex of a far
+// triangle, which the reference's unbounded sweep does visit, can lie right in front of the sphere.
+// (Found by a 256-world soak: one agent-step in 1.4 million.)  A mirrored vertex can be hit below the bound
+// only if some v lies within sphere_r of the segment 2 ray_o + t ray_d, t in [0, t_bound]; this
+// returns false when the vertex occupancy grid (x, y only: conservative) has no vertex near that
+// segment, and the callers drop the bound otherwise.
+MP_HD bool sphereSweepMayTouchMirroredVertex(const MapConsts &mc, Vec3 ray_o, Vec3 ray_d, float t_bound, float sphere_r)
+{
+    const float pad = sphere_r + 1.f;
+    const float ax = 2.f * ray_o.x, ay = 2.f * ray_o.y;
+    const float bx = ax + ray_d.x * t_bound, by = ay + ray_d.y * t_bound;
+    const float x0 = fminf(ax, bx) - pad, x1 = fmaxf(ax, bx) + pad;
+    const float y0 = fminf(ay, by) - pad, y1 = fmaxf(ay, by) + pad;
+    const float fi0 = (x0 - mc.vertGridMinX) * mc.vertGridInvCellX, fi1 = (x1 - mc.vertGridMinX) * mc.vertGridInvCellX;
+    const float fj0 = (y0 - mc.vertGridMinY) * mc.vertGridInvCellY, fj1 = (y1 - mc.vertGridMinY) * mc.vertGridInvCellY;
+    if (!(fi1 >= 0.f && fj1 >= 0.f && fi0 < (float)kVertGrid && fj0 < (float)kVertGrid)) {
+        // outside the grid -- or not comparable (NaN): be safe
+        return !(fi1 < 0.f || fj1 < 0.f || fi0 >= (float)kVertGrid || fj0 >= (float)kVertGrid);
+    }
+    // vertices on the upper border are clamped into the last cell (assets.cpp)
+    const int i0 = fi0 < 0.f ? 0 : (int)fi0, i1 = fi1 >= (float)kVertGrid ? kVertGrid - 1 : (int)fi1;
+    const int j0 = fj0 < 0.f ? 0 : (int)fj0, j1 = fj1 >= (float)kVertGrid ? kVertGrid - 1 : (int)fj1;
+    for (int j = j0; j <= j1; j++)
+        for (int i = i0; i <= i1; i++)
+            if ((mc.vertGrid[(j * kVertGrid + i) >> 5] >> ((j * kVertGrid + i) & 31)) & 1u) return true;
+    return false;
+}
+
+// A sweep of which the caller only distinguishes hits below `bound`: bounded where that is provably the
+// reference's answer, else the reference's unbounded loop.  *out_n untouched on a miss.
+template <typename BVH>
+MP_HD_NOINLINE float sphereSweepBelow(const BVH &bvh, const MapConsts &mc, Vec3 ray_o, Vec3 ray_d, float sphere_r, Vec3 *out_n,
+                             float bound)
+{
+    if (!sphereSweepMayTouchMirroredVertex(mc, ray_o, ray_d, bound, sphere_r)) {
+        bool risky = false;
+        Vec3 n = *out_n;
+        const float t = bvhSphereCast(bvh, ray_o, ray_d, sphere_r, &n, bound, &risky);
+        if (!risky) { *out_n = n; return t; }
+    }
+    return bvhSphereCast(bvh, ray_o, ray_d, sphere_r, out_n);
 }
 
 }  // namespace mpenv

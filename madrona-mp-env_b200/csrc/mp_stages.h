@@ -139,7 +139,7 @@ MP_HD Vec3 rotate2D(Vec3 dir, float radians)
 // compiled out).
 // BVH: BVHView (reference format) or SphereBVH (sphere_fast.cuh) -- bvhSphereCast is overloaded.
 template <typename BVH>
-MP_HD void applyVelocitySystem(const BVH &bvh, Vec3 pos, Vec3 vel, int32_t cur_pose,
+MP_HD void applyVelocitySystem(const BVH &bvh, const MapConsts &mc, Vec3 pos, Vec3 vel, int32_t cur_pose,
                                MoveState &move)
 {
     Vec3 x = pos;
@@ -173,16 +173,17 @@ MP_HD void applyVelocitySystem(const BVH &bvh, Vec3 pos, Vec3 vel, int32_t cur_p
 
     // Everything below uses the forward casts only through fmaxf(0, t - buffer) compared
     // with / clamped to move_dist (and t == 0), so hits past move_dist + buffer are misses.
+    // (Bounded only where that is exact: sphereSweepBelow, mp_geom.h.)
     const float fwd_bound = (move_dist + buffer) * 1.001f + 0.01f;
     ray_o = x + v_norm * buffer * 0.5f;
     ray_o.z += low_check_height;
-    float low_dist = bvhSphereCast(bvh, ray_o, v_norm, r, &normal, fwd_bound);
+    float low_dist = sphereSweepBelow(bvh, mc, ray_o, v_norm, r, &normal, fwd_bound);
     float high_dist = low_dist;
     bool high_hit = false;
     if (cur_pose != 2) {
         ray_o.z = x.z + top_of_capsule;
         Vec3 high_normal = v3(0, 0, 0);
-        high_dist = bvhSphereCast(bvh, ray_o, v_norm, r, &high_normal, fwd_bound);
+        high_dist = sphereSweepBelow(bvh, mc, ray_o, v_norm, r, &high_normal, fwd_bound);
         if (high_dist < low_dist) {
             low_dist = high_dist;
             normal = high_normal;
@@ -199,10 +200,10 @@ MP_HD void applyVelocitySystem(const BVH &bvh, Vec3 pos, Vec3 vel, int32_t cur_p
         if (dot(slide_dir, v_norm) < 0) slide_dir = -slide_dir;
         ray_o = x + v_norm * low_dist;
         ray_o.z += high_hit ? top_of_capsule : low_check_height;
-        Vec3 tmp_n;
+        Vec3 tmp_n = v3(0, 0, 0);
         float max_move = move_dist - low_dist;
         // clamped to max_move below: same argument
-        float slide_dist = bvhSphereCast(bvh, ray_o, slide_dir, r, &tmp_n, (max_move + buffer) * 1.001f + 0.01f);
+        float slide_dist = sphereSweepBelow(bvh, mc, ray_o, slide_dir, r, &tmp_n, (max_move + buffer) * 1.001f + 0.01f);
         slide_dist = fmaxf(0.0f, slide_dist - buffer);
         slide_dist = fminf(slide_dist, max_move);
         if (slide_dist > 0.0f) hit_pos = hit_pos + slide_dir * slide_dist;
@@ -285,7 +286,7 @@ MP_HD void stageMove(const Ctx &c, const BVH &bvh, int idx)
     stageBot(c, idx);            // policy id -1: plan + apply the scripted bot's action rows
     movementSystem(p.actDiscrete[idx], rot, vel, alive, combat, stand, move);
     aimSystems(p.actAim[idx], p.actDiscreteAim[idx], rot, aim, alive);
-    applyVelocitySystem(bvh, pos, vel, stand.cur, move);
+    applyVelocitySystem(bvh, *c.mc, pos, vel, stand.cur, move);
     pos = move.newPos;          // updateMoveStateSystem (sim.cpp:1030-1039)
     vel = move.newVel;
     fallSystem(bvh, pos, move, alive);

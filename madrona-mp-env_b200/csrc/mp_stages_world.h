@@ -1127,6 +1127,10 @@ MP_HD void initWorld(const Ctx &c, int w, bool triggered_reset)
         cs.wasKilled = 0;
         cs.firedShotT = -FLT_MAX;
         cs.hasDiedDuringEpisode = 0;
+        // The reference builds this CombatState in an UNINITIALISED local (level_gen.cpp:343-355): reloadedFullMag
+        // (like inZone / minDistToZone, which zoneSystem rewrites before any use) is whatever the stack held --
+        // zero in every build of the oracle observed.  Nothing reads it before fireSystem clears it next step.
+        cs.reloadedFullMag = 0;
         p.alive[idx] = 0.f;
         OpponentObs zero_ob;
         {

@@ -95,9 +95,33 @@ __device__ __forceinline__ SphereBVH stageSphereBVH(const uint4 *image, uint32_t
     return f;
 }
 
-// bvhSphereCast (mp_geom.h) on the staged nodes: same visiting order, same t_bound contract.
-__device__ __noinline__ float bvhSphereCast(const SphereBVH &bvh, Vec3 ray_o, Vec3 ray_d, float sphere_r,
-                                            Vec3 *out_n, float t_bound = FLT_MAX)
+// The grown box of child i (the staged bounds are expanded by the radius already): is it entered before
+// t_bound, and does the sweep meet the child's own box at all?  Detection only (kSweepSlack, mp_geom.h):
+// plain arithmetic, no parity with anything.
+__device__ __forceinline__ bool sphereChildGrownHit(const char *nd, int i, uint32_t offX, uint32_t offY, uint32_t offZ,
+                                                    Vec3 o, Vec3 inv_d, float t_bound, bool need_own_box)
+{
+    const float2 bx = *reinterpret_cast<const float2 *>(nd + offX + 8 * i);
+    const float2 by = *reinterpret_cast<const float2 *>(nd + offY + 8 * i);
+    const float2 bz = *reinterpret_cast<const float2 *>(nd + offZ + 8 * i);
+    if (need_own_box) {
+        const float tn = fmaxf(fmaxf(fmaxf(0.f, (bx.x - o.x) * inv_d.x), (by.x - o.y) * inv_d.y), (bz.x - o.z) * inv_d.z);
+        const float tf = fminf(fminf((bx.y - o.x) * inv_d.x, (by.y - o.y) * inv_d.y), (bz.y - o.z) * inv_d.z);
+        if (!(tn < tf)) return false;
+    }
+    // near moves outwards against the direction of travel, far along it
+    const float sx = copysignf(kSweepSlack, inv_d.x), sy = copysignf(kSweepSlack, inv_d.y), sz = copysignf(kSweepSlack, inv_d.z);
+    const float tn = fmaxf(fmaxf(fmaxf(0.f, ((bx.x - sx) - o.x) * inv_d.x), ((by.x - sy) - o.y) * inv_d.y), ((bz.x - sz) - o.z) * inv_d.z);
+    const float tf = fminf(fminf(((bx.y + sx) - o.x) * inv_d.x, ((by.y + sy) - o.y) * inv_d.y), ((bz.y + sz) - o.z) * inv_d.z);
+    return tn < fminf(tf, t_bound);
+}
+
+// bvhSphereCast (mp_geom.h) on the staged nodes: same visiting order, same t_bound / risky contract.
+// kDetect: the bounded form with detection (two or three of an agent's casts); the plain form -- the
+// vertical casts, and the unbounded repeat of a risky one -- carries none of that code.
+template <bool kDetect>
+__device__ __noinline__ float sphereCastStaged(const SphereBVH &bvh, Vec3 ray_o, Vec3 ray_d, float sphere_r,
+                                               Vec3 *out_n, float t_bound, bool *risky)
 {
     MP_COUNT_RAYS(3, 1);
     const Vec3 inv_d = v3(1.f / ray_d.x, 1.f / ray_d.y, 1.f / ray_d.z);
@@ -105,6 +129,8 @@ __device__ __noinline__ float bvhSphereCast(const SphereBVH &bvh, Vec3 ray_o, Ve
     const uint32_t offX = (uint32_t)offsetof(SphereNode, b) + (f2u(inv_d.x) >> 31) * 32u;
     const uint32_t offY = (uint32_t)offsetof(SphereNode, b) + 64u + (f2u(inv_d.y) >> 31) * 32u;
     const uint32_t offZ = (uint32_t)offsetof(SphereNode, b) + 128u + (f2u(inv_d.z) >> 31) * 32u;
+    constexpr int32_t kDetectOnly = 0x40000000;
+    bool flagged = false;            // kDetect: a (mis)reported feature hit below the bound is possible
     int32_t stack[32];
     int32_t stack_size = 0;
     stack[stack_size++] = 0;
@@ -112,10 +138,30 @@ __device__ __noinline__ float bvhSphereCast(const SphereBVH &bvh, Vec3 ray_o, Ve
     const float t_max = t_bound;
     float hit_t = t_max;
     while (stack_size > 0) {
-        const char *nd = reinterpret_cast<const char *>(bvh.nodes + stack[--stack_size]);
+        const int32_t entry = stack[--stack_size];
+        const char *nd = reinterpret_cast<const char *>(bvh.nodes + (entry & ~kDetectOnly));
         const int4 ch = *reinterpret_cast<const int4 *>(nd);
         const int32_t child[4] = { ch.x, ch.y, ch.z, ch.w };
+        if (kDetect && (entry & kDetectOnly)) {
+            // a subtree the bound culled: only whether a feature test inside could fire before the bound
+            for (int i = 0; i < 4; i++) {
+                if (child[i] == kBVHSentinel || flagged) continue;
+                if (!sphereChildGrownHit(nd, i, offX, offY, offZ, ray_o, inv_d, t_max, true)) continue;
+                if (child[i] & 0x80000000) {
+                    const int32_t leaf_idx = child[i] & ~0x80000000;
+                    for (int k = 0; k < 2; k++) {
+                        const Vec3 *tv = bvh.verts + (size_t)(leaf_idx + k) * 3;
+                        if (sphereCastFeaturesBefore(tv[0], tv[1], tv[2], ray_o, ray_d, t_max, sphere_r)) flagged = true;
+                    }
+                } else {
+                    stack[stack_size++] = child[i] | kDetectOnly;
+                }
+            }
+            continue;
+        }
         float tn[4], tf[4];
+        float tg[4];                 // kDetect: entry into the child's box grown by the slack (branch-free, with the rest)
+        const float gx = copysignf(kSweepSlack, inv_d.x), gy = copysignf(kSweepSlack, inv_d.y), gz = copysignf(kSweepSlack, inv_d.z);
         {
             const float4 *px = reinterpret_cast<const float4 *>(nd + offX);
             const float4 *py = reinterpret_cast<const float4 *>(nd + offY);
@@ -135,19 +181,41 @@ __device__ __noinline__ float bvhSphereCast(const SphereBVH &bvh, Vec3 ray_o, Ve
                 // the far side is folded onto the running hit distance at the child's turn (below)
                 tf[2 * h] = fminf(fminf(fx0, fy0), fz0);
                 tf[2 * h + 1] = fminf(fminf(fx1, fy1), fz1);
+                if (kDetect) {
+                    tg[2 * h] = fmaxf(fmaxf(fmaxf(0.f, ((bx.x - gx) - ray_o.x) * inv_d.x), ((by.x - gy) - ray_o.y) * inv_d.y),
+                                      ((bz.x - gz) - ray_o.z) * inv_d.z);
+                    tg[2 * h + 1] = fmaxf(fmaxf(fmaxf(0.f, ((bx.z - gx) - ray_o.x) * inv_d.x), ((by.z - gy) - ray_o.y) * inv_d.y),
+                                          ((bz.z - gz) - ray_o.z) * inv_d.z);
+                }
             }
         }
 #pragma unroll
         for (int i = 0; i < 4; i++) {
             if (child[i] == kBVHSentinel) continue;
-            if (!(tn[i] < fminf(tf[i], hit_t))) continue;
+            if (!(tn[i] < fminf(tf[i], hit_t))) {
+                // culled by the bound alone (the sweep does meet the box, and nothing was hit yet)?
+                if (kDetect && hit_t == t_max && tn[i] < tf[i] && tg[i] < t_max && !flagged) {
+                    if (child[i] & 0x80000000) {
+                        const int32_t leaf_idx = child[i] & ~0x80000000;
+                        for (int k = 0; k < 2; k++) {
+                            const Vec3 *tv = bvh.verts + (size_t)(leaf_idx + k) * 3;
+                            if (sphereCastFeaturesBefore(tv[0], tv[1], tv[2], ray_o, ray_d, t_max, sphere_r)) flagged = true;
+                        }
+                    } else {
+                        stack[stack_size++] = child[i] | kDetectOnly;
+                    }
+                }
+                continue;
+            }
             if (child[i] & 0x80000000) {
                 const int32_t leaf_idx = child[i] & ~0x80000000;
                 Vec3 leaf_n = v3(0.f, 0.f, 0.f);
                 float leaf_t = hit_t;
                 for (int k = 0; k < 2; k++) {
                     const Vec3 *tv = bvh.verts + (size_t)(leaf_idx + k) * 3;
-                    leaf_t = sphereCastTriangle(tv[0], tv[1], tv[2], ray_o, ray_d, leaf_t, sphere_r, &leaf_n);
+                    const float t = sphereCastTriangle(tv[0], tv[1], tv[2], ray_o, ray_d, leaf_t, sphere_r, &leaf_n, kDetect);
+                    if (kDetect && t < 0.f) flagged = true;       // kSweepRisky: leaf_t stays
+                    else leaf_t = t;
                 }
                 if (leaf_t < hit_t) { hit_t = leaf_t; closest_n = leaf_n; }
             } else {
@@ -155,8 +223,16 @@ __device__ __noinline__ float bvhSphereCast(const SphereBVH &bvh, Vec3 ray_o, Ve
             }
         }
     }
+    if (kDetect && flagged) *risky = true;
     if (hit_t < t_max) *out_n = closest_n;
     return hit_t < t_max ? hit_t : FLT_MAX;
+}
+
+__device__ __forceinline__ float bvhSphereCast(const SphereBVH &bvh, Vec3 ray_o, Vec3 ray_d, float sphere_r,
+                                               Vec3 *out_n, float t_bound = FLT_MAX, bool *risky = nullptr)
+{
+    if (risky != nullptr && t_bound < FLT_MAX) return sphereCastStaged<true>(bvh, ray_o, ray_d, sphere_r, out_n, t_bound, risky);
+    return sphereCastStaged<false>(bvh, ray_o, ray_d, sphere_r, out_n, t_bound, nullptr);
 }
 
 }  // namespace mpenv

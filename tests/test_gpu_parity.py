@@ -322,6 +322,42 @@ def test_pipelined_readback_equals_sync_read():
         a_.close(); b_.close()
 
 
+def test_soak_256_worlds_grazing_wall():
+    """256 worlds x 520 steps, seek / random policy phases as tools/soak.py: at step 462 world 165 holds the
+    grazing-wall case of test_hostsim_parity.py::test_grazing_wall_bounded_sweep_regression (bounded sweeps
+    must detect it and fall back to the reference's unbounded loop)."""
+    W = 256
+    gpu = S.GpuSim(W, auto_reset=True, full_team=False)
+    orc = S.Oracle(W, auto_reset=True, det=True, num_threads=0)
+    try:
+        gpu.init(); orc.init()
+        for s in range(520):
+            d, a = S.seek_policy(orc, s, W) if (s // 100) % 2 == 0 else S.random_actions(s, W)
+            for sim in (gpu, orc):
+                sim.set_actions(d, a); sim.step()
+            if s % 50 == 49 or 460 <= s <= 464:
+                assert_same(gpu, orc, W, f"step {s}", full_team=False)
+    finally:
+        gpu.close(); orc.close()
+
+
+def test_episode_end_with_random_actions_gpu():
+    """See test_hostsim_parity.py::test_episode_end_with_random_actions: a whole 3000-step episode and its auto-reset."""
+    W = 8
+    gpu = S.GpuSim(W, auto_reset=True, full_team=False)
+    orc = S.Oracle(W, auto_reset=True, det=True, num_threads=0)
+    try:
+        gpu.init(); orc.init()
+        for s in range(3004):
+            d, a = S.random_actions(s, W)
+            for sim in (gpu, orc):
+                sim.set_actions(d, a); sim.step()
+            if s % 500 == 499 or s >= 2996:
+                assert_same(gpu, orc, W, f"step {s}", full_team=False)
+    finally:
+        gpu.close(); orc.close()
+
+
 @pytest.mark.parametrize("W", [1, 3, 37, 700])
 def test_lidar_packets_vs_oracle(W):
     """k_lidar_packet (five 32-ray packets per 2-agent task, tasks drawn from a device-wide counter,

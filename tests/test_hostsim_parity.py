@@ -70,6 +70,45 @@ def test_larger_map(built, tmp_path):
         host.close(); orc.close()
 
 
+def test_grazing_wall_bounded_sweep_regression(built):
+    """World 165 of the 256-world soak (tools/soak.py), step 462: an agent slides along a 1300-unit wall at
+    15.008 units and the reference's edge test reports the wall's diagonal at t = 6.88 although the sphere
+    reaches the wall's plane at t = 7.16 -- inside the step's reach, where a sweep that was simply bounded at the
+    distance the step can use returned a miss (mp_geom.h: kSweepSlack, sphereSweepBelow)."""
+    W, off = 1, 165
+    host = S.HostSim(W, auto_reset=True, full_team=False, world_id_offset=off)
+    orc = S.Oracle(W, auto_reset=True, det=True, num_threads=1, world_id_offset=off)
+    try:
+        host.init(); orc.init()
+        for s in range(470):
+            d, a = S.seek_policy(orc, s, W, world_id_offset=off) if (s // 100) % 2 == 0 else S.random_actions(s, W, off)
+            for sim in (host, orc):
+                sim.set_actions(d, a); sim.step()
+            if s >= 455:
+                assert_same(host, orc, W, f"step {s}", full_team=False)
+    finally:
+        host.close(); orc.close()
+
+
+def test_episode_end_with_random_actions(built):
+    """A full 3000-step episode under random actions, then the auto-reset: a third of the agents reload with a full
+    magazine on any step, so CombatState::reloadedFullMag is set when initWorld rebuilds the agents (the reference
+    leaves that field uninitialised there, level_gen.cpp:343-355; the oracle builds read it as 0)."""
+    W = 2
+    host = S.HostSim(W, auto_reset=True, full_team=False)
+    orc = S.Oracle(W, auto_reset=True, det=True, num_threads=0)
+    try:
+        host.init(); orc.init()
+        for s in range(3004):
+            d, a = S.random_actions(s, W)
+            for sim in (host, orc):
+                sim.set_actions(d, a); sim.step()
+            if s % 500 == 499 or s >= 2996:
+                assert_same(host, orc, W, f"step {s}", full_team=False)
+    finally:
+        host.close(); orc.close()
+
+
 def random_policy(sim, s, W):
     return S.random_actions(s, W)
 
