@@ -124,6 +124,12 @@ __device__ __noinline__ float sphereCastStaged(const SphereBVH &bvh, Vec3 ray_o,
                                                Vec3 *out_n, float t_bound, bool *risky)
 {
     MP_COUNT_RAYS(3, 1);
+    // the staged image lives in shared memory: say so, or this (non-inlined) function reads it through
+    // generic loads (LD + R2UR instead of LDS: 2 M more instructions per launch)
+    const SphereNode *const nodes = bvh.nodes;
+    const Vec3 *const verts = bvh.verts;
+    __builtin_assume(__isShared(nodes));
+    __builtin_assume(__isShared(verts));
     const Vec3 inv_d = v3(1.f / ray_d.x, 1.f / ray_d.y, 1.f / ray_d.z);
     // byte offset of each axis's (near, far) order inside a node
     const uint32_t offX = (uint32_t)offsetof(SphereNode, b) + (f2u(inv_d.x) >> 31) * 32u;
@@ -139,7 +145,7 @@ __device__ __noinline__ float sphereCastStaged(const SphereBVH &bvh, Vec3 ray_o,
     float hit_t = t_max;
     while (stack_size > 0) {
         const int32_t entry = stack[--stack_size];
-        const char *nd = reinterpret_cast<const char *>(bvh.nodes + (entry & ~kDetectOnly));
+        const char *nd = reinterpret_cast<const char *>(nodes + (entry & ~kDetectOnly));
         const int4 ch = *reinterpret_cast<const int4 *>(nd);
         const int32_t child[4] = { ch.x, ch.y, ch.z, ch.w };
         if (kDetect && (entry & kDetectOnly)) {
@@ -150,7 +156,7 @@ __device__ __noinline__ float sphereCastStaged(const SphereBVH &bvh, Vec3 ray_o,
                 if (child[i] & 0x80000000) {
                     const int32_t leaf_idx = child[i] & ~0x80000000;
                     for (int k = 0; k < 2; k++) {
-                        const Vec3 *tv = bvh.verts + (size_t)(leaf_idx + k) * 3;
+                        const Vec3 *tv = verts + (size_t)(leaf_idx + k) * 3;
                         if (sphereCastFeaturesBefore(tv[0], tv[1], tv[2], ray_o, ray_d, t_max, sphere_r)) flagged = true;
                     }
                 } else {
@@ -198,7 +204,7 @@ __device__ __noinline__ float sphereCastStaged(const SphereBVH &bvh, Vec3 ray_o,
                     if (child[i] & 0x80000000) {
                         const int32_t leaf_idx = child[i] & ~0x80000000;
                         for (int k = 0; k < 2; k++) {
-                            const Vec3 *tv = bvh.verts + (size_t)(leaf_idx + k) * 3;
+                            const Vec3 *tv = verts + (size_t)(leaf_idx + k) * 3;
                             if (sphereCastFeaturesBefore(tv[0], tv[1], tv[2], ray_o, ray_d, t_max, sphere_r)) flagged = true;
                         }
                     } else {
@@ -212,7 +218,7 @@ __device__ __noinline__ float sphereCastStaged(const SphereBVH &bvh, Vec3 ray_o,
                 Vec3 leaf_n = v3(0.f, 0.f, 0.f);
                 float leaf_t = hit_t;
                 for (int k = 0; k < 2; k++) {
-                    const Vec3 *tv = bvh.verts + (size_t)(leaf_idx + k) * 3;
+                    const Vec3 *tv = verts + (size_t)(leaf_idx + k) * 3;
                     const float t = sphereCastTriangle(tv[0], tv[1], tv[2], ray_o, ray_d, leaf_t, sphere_r, &leaf_n, kDetect);
                     if (kDetect && t < 0.f) flagged = true;       // kSweepRisky: leaf_t stays
                     else leaf_t = t;
