@@ -94,9 +94,9 @@ def test_episode_end_with_random_actions(built):
     """A full 3000-step episode under random actions, then the auto-reset: a third of the agents reload with a full
     magazine on any step, so CombatState::reloadedFullMag is set when initWorld rebuilds the agents (the reference
     leaves that field uninitialised there, level_gen.cpp:343-355; the oracle builds read it as 0)."""
-    W = 2
+    W = 1
     host = S.HostSim(W, auto_reset=True, full_team=False)
-    orc = S.Oracle(W, auto_reset=True, det=True, num_threads=0)
+    orc = S.Oracle(W, auto_reset=True, det=True, num_threads=1)
     try:
         host.init(); orc.init()
         for s in range(3004):
@@ -114,10 +114,10 @@ def random_policy(sim, s, W):
 
 
 def test_random_actions_parity_run(built):
-    """BASELINE.json configs[0] at its full length (random actions, 1000 steps) on 12 worlds: the stage
+    """BASELINE.json configs[0] at its full length (random actions, 1000 steps) on 8 worlds: the stage
     functions run single-threaded on the host; the 32-world run is the GPU test's
     (test_gpu_parity.py::test_random_actions_32_worlds_bit_exact)."""
-    rollout(12, 1000, random_policy, check_every=100)
+    rollout(8, 1000, random_policy, check_every=100)
 
 
 def test_combat_policy(built):
