@@ -166,7 +166,7 @@ __device__ __noinline__ float sphereCastStaged(const SphereBVH &bvh, Vec3 ray_o,
             continue;
         }
         float tn[4], tf[4];
-        float tg[4];                 // kDetect: entry into the child's box grown by the slack (branch-free, with the rest)
+        uint32_t grown = 0;          // kDetect: bit i = child i's box, grown by the slack, is entered before the bound
         const float gx = copysignf(kSweepSlack, inv_d.x), gy = copysignf(kSweepSlack, inv_d.y), gz = copysignf(kSweepSlack, inv_d.z);
         {
             const float4 *px = reinterpret_cast<const float4 *>(nd + offX);
@@ -188,10 +188,11 @@ __device__ __noinline__ float sphereCastStaged(const SphereBVH &bvh, Vec3 ray_o,
                 tf[2 * h] = fminf(fminf(fx0, fy0), fz0);
                 tf[2 * h + 1] = fminf(fminf(fx1, fy1), fz1);
                 if (kDetect) {
-                    tg[2 * h] = fmaxf(fmaxf(fmaxf(0.f, ((bx.x - gx) - ray_o.x) * inv_d.x), ((by.x - gy) - ray_o.y) * inv_d.y),
-                                      ((bz.x - gz) - ray_o.z) * inv_d.z);
-                    tg[2 * h + 1] = fmaxf(fmaxf(fmaxf(0.f, ((bx.z - gx) - ray_o.x) * inv_d.x), ((by.z - gy) - ray_o.y) * inv_d.y),
-                                          ((bz.z - gz) - ray_o.z) * inv_d.z);
+                    const float g0 = fmaxf(fmaxf(fmaxf(0.f, ((bx.x - gx) - ray_o.x) * inv_d.x), ((by.x - gy) - ray_o.y) * inv_d.y),
+                                           ((bz.x - gz) - ray_o.z) * inv_d.z);
+                    const float g1 = fmaxf(fmaxf(fmaxf(0.f, ((bx.z - gx) - ray_o.x) * inv_d.x), ((by.z - gy) - ray_o.y) * inv_d.y),
+                                           ((bz.z - gz) - ray_o.z) * inv_d.z);
+                    grown |= (g0 < t_max ? 1u : 0u) << (2 * h) | (g1 < t_max ? 2u : 0u) << (2 * h);
                 }
             }
         }
@@ -200,7 +201,7 @@ __device__ __noinline__ float sphereCastStaged(const SphereBVH &bvh, Vec3 ray_o,
             if (child[i] == kBVHSentinel) continue;
             if (!(tn[i] < fminf(tf[i], hit_t))) {
                 // culled by the bound alone (the sweep does meet the box, and nothing was hit yet)?
-                if (kDetect && hit_t == t_max && tn[i] < tf[i] && tg[i] < t_max && !flagged) {
+                if (kDetect && ((grown >> i) & 1u) && hit_t == t_max && tn[i] < tf[i] && !flagged) {
                     if (child[i] & 0x80000000) {
                         const int32_t leaf_idx = child[i] & ~0x80000000;
                         for (int k = 0; k < 2; k++) {
